@@ -1,0 +1,256 @@
+"""``python -m azure_hc_intel_tf_b200.cli.cnn_benchmarks`` — the tf_cnn_benchmarks.py role.
+
+The reference runs ``python tf_cnn_benchmarks.py $TF_ARGS`` under mpirun
+(benchmark-scripts/run-tf-sing-ucx-openmpi.sh:99-109) with the 19 flags at :62-81: 50 warm-up batches,
+100 timed batches, a line every 10 steps, momentum SGD, Horovod variable update. This module accepts the
+same flags, prints the same header / step lines / ``total images/sec`` summary, and drives the B200 stack.
+
+Timing is on the device: one CUDA event per step boundary on the compute stream; the per-rank time of the
+timed region is reduced with MAX over ranks before images/sec is computed.
+"""
+from __future__ import annotations
+
+import json
+import sys
+import time
+from typing import List, Optional
+
+import torch
+
+from .. import hvd, models, ops
+from ..ops import data as data_mod
+from ..utils import ckpt, flags as flags_mod, log
+from ..utils.timeline import Timeline
+
+
+class BenchmarkCNN:
+    def __init__(self, params: flags_mod.Params, data_source: str = "device"):
+        self.p = params
+        p = params
+        self.use_hvd = p.variable_update == "horovod"
+        want_cuda = p.device == "gpu" and torch.cuda.is_available()
+        if p.device == "gpu" and not torch.cuda.is_available():
+            raise SystemExit("--device=gpu but no CUDA device is visible (use --device=cpu for the plumbing path)")
+        fabric = p.fabric
+        if fabric == "auto":
+            fabric = "nvl" if want_cuda else "gloo"
+        if self.use_hvd:
+            hvd.init(fabric=fabric, device="cuda" if want_cuda else "cpu")
+            self.world, self.rank = hvd.size(), hvd.rank()
+            self.device = hvd.device()
+            self.fabric = hvd.fabric()
+        else:
+            self.world, self.rank = 1, 0
+            self.device = torch.device("cuda", torch.cuda.current_device()) if want_cuda else torch.device("cpu")
+            self.fabric = "none"
+        self.kernels = p.kernels
+        if self.kernels == "auto":
+            self.kernels = "b200" if want_cuda else "cudnn"
+        if self.kernels == "b200" and not want_cuda:
+            raise SystemExit("--kernels=b200 needs a B200; use --kernels=cudnn on CPU")
+        self.dtype = torch.bfloat16 if (p.use_fp16 and want_cuda) else torch.float32
+        torch.manual_seed(p.seed)
+        self.model = models.create_model(p.model, kernels=self.kernels)
+        self.batch = p.batch_size or self.model.default_batch_size
+        self.global_batch = self.batch * self.world
+        self.model.to(self.device)
+        self.model.train(not p.forward_only)
+        self.warmup = p.num_warmup_batches if p.num_warmup_batches is not None else max(10, min(50, p.num_batches))
+        self.lr = p.init_learning_rate if p.init_learning_rate is not None else self.model.get_learning_rate(self.global_batch)
+        self.timeline = Timeline(p.timeline, self.rank) if p.timeline else None
+        self.opt = None if p.forward_only else self._make_optimizer()
+        self.global_step = 0
+        if p.train_dir:
+            self.global_step = ckpt.restore(p.train_dir, self.model, self.opt)
+            if self.global_step and self.rank == 0:
+                print(f"Restored checkpoint at global_step {self.global_step} from {p.train_dir}")
+        if self.use_hvd and self.world > 1:
+            # Horovod's broadcast_global_variables(0)
+            hvd.broadcast_parameters(self.model.state_dict(), root_rank=0)
+            if self.opt is not None:
+                hvd.broadcast_optimizer_state(self.opt, root_rank=0)
+        src = data_mod.HostSynthetic if data_source == "host" else data_mod.DeviceSynthetic
+        self.data = src(self.batch, self.model.image_size, self.model.cfg.num_classes, self.device, self.dtype,
+                        seed=p.seed + self.rank)
+        self._graph = None
+        self._last_save = time.time()
+
+    # ------------------------------------------------------------------ set-up
+    def _make_optimizer(self):
+        p = self.p
+        named = [(n, q) for n, q in self.model.named_parameters() if q.requires_grad]
+        thr = flags_mod.resolve_fusion_threshold(p)
+        native = p.optimizer in ("momentum", "sgd", "lars") and not (self.kernels == "cudnn" and self.fabric == "nccl")
+        if native:
+            mu = 0.0 if p.optimizer == "sgd" else p.momentum
+            opt = hvd.MomentumSGD(named, lr=self.lr, momentum=mu, weight_decay=p.weight_decay,
+                                  lars=p.optimizer == "lars", lars_eta=p.lars_eta,
+                                  lowp=self.kernels == "b200", fusion_threshold=thr)
+        else:
+            # stock-library baseline (and rmsprop / adam): torch.optim on the fp32 parameters
+            ps = [q for _, q in named]
+            if p.optimizer in ("momentum", "sgd", "lars"):
+                opt = torch.optim.SGD(ps, lr=self.lr, momentum=0.0 if p.optimizer == "sgd" else p.momentum,
+                                      weight_decay=p.weight_decay)
+            elif p.optimizer == "rmsprop":
+                opt = torch.optim.RMSprop(ps, lr=self.lr, alpha=0.9, momentum=p.momentum, eps=1.0,
+                                          weight_decay=p.weight_decay)
+            else:
+                opt = torch.optim.Adam(ps, lr=self.lr, weight_decay=p.weight_decay)
+        if self.use_hvd:
+            opt = hvd.DistributedOptimizer(opt, named_parameters=named, fusion_threshold=thr, timeline=self.timeline)
+        return opt
+
+    # ------------------------------------------------------------------ one step
+    def forward_loss(self, images, labels):
+        if self.kernels == "cudnn" and self.dtype == torch.bfloat16:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                logits = self.model(images)
+        else:
+            logits = self.model(images)
+        return ops.softmax_cross_entropy(logits, labels, self.model.cfg), logits
+
+    def train_step(self, images, labels):
+        if self.p.forward_only:
+            with torch.no_grad():
+                loss, _ = self.forward_loss(images, labels)
+            return loss
+        self.opt.zero_grad(set_to_none=not hasattr(self.opt, "plan"))
+        loss, _ = self.forward_loss(images, labels)
+        loss.backward()
+        self.opt.step()
+        self.global_step += 1
+        return loss
+
+    def step(self):
+        images, labels = self.data.next()
+        return self.train_step(images, labels)
+
+    # ------------------------------------------------------------------ reporting
+    def print_info(self):
+        if self.rank != 0:
+            return
+        p = self.p
+        dev = "gpu" if self.device.type == "cuda" else "cpu"
+        devices = [f"horovod/{dev}:{i}" for i in range(self.world)] if self.use_hvd else [f"/{dev}:0"]
+        n_img = 1281167
+        extra = []
+        if self.use_hvd:
+            extra.append(f"Horovod on:  {dev}")
+            extra.append(f"Fabric:      {self.fabric}")
+        extra.append(f"Kernels:     {self.kernels}")
+        extra.append(f"Precision:   {'bf16' if self.dtype == torch.bfloat16 else 'fp32'}")
+        lines = log.header_lines(self.model.name, "imagenet (synthetic)",
+                                 "forward-only" if p.forward_only else "training", self.global_batch, self.batch,
+                                 p.num_batches, p.num_batches * self.global_batch / n_img, devices,
+                                 "NHWC" if self.device.type == "cuda" else p.data_format, p.optimizer,
+                                 p.variable_update, extra)
+        for note in p.notes:
+            print("Note:", note)
+        print("\n".join(lines))
+
+    def total_loss(self, xent: torch.Tensor) -> float:
+        v = float(xent.detach().float().item())
+        if not self.p.forward_only and self.p.weight_decay > 0:
+            v += float(ops.l2_loss([q for q in self.model.parameters() if q.requires_grad and getattr(q, "decay", True)],
+                                   self.p.weight_decay).item())
+        return v
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+
+    def _barrier(self):
+        if self.use_hvd and self.world > 1:
+            hvd.barrier()
+
+    def run(self) -> dict:
+        p = self.p
+        self.print_info()
+        cuda = self.device.type == "cuda"
+        if self.rank == 0:
+            print("Running warm up")
+        for _ in range(self.warmup):
+            loss = self.step()
+        self._sync()
+        self._barrier()
+        self._sync()
+        if self.rank == 0:
+            print("Done warm up")
+            print(log.table_header())
+        events: List = []
+        wall: List[float] = []
+        step_times: List[float] = []
+        losses = []
+
+        def mark():
+            if cuda:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                events.append(e)
+            else:
+                wall.append(time.perf_counter())
+
+        mark()
+        last_reported = 0
+        for i in range(1, p.num_batches + 1):
+            loss = self.step()
+            mark()
+            if i % p.display_every == 0 or i == p.num_batches:
+                self._sync()
+                if cuda:
+                    step_times += [events[j].elapsed_time(events[j + 1]) / 1e3 for j in range(last_reported, i)]
+                else:
+                    step_times += [wall[j + 1] - wall[j] for j in range(last_reported, i)]
+                last_reported = i
+                tl = self.total_loss(loss)
+                losses.append(tl)
+                if self.rank == 0:
+                    print(log.step_line(i, self.global_batch, step_times, tl), flush=True)
+            self._maybe_save()
+        self._sync()
+        total_s = sum(step_times)
+        if self.use_hvd and self.world > 1:
+            t = torch.tensor([total_s], dtype=torch.float64, device=self.device if self.fabric != "gloo" else "cpu")
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            total_s = float(t.item())
+        self._barrier()
+        ips = p.num_batches * self.global_batch / total_s if total_s > 0 else 0.0
+        if self.rank == 0:
+            print("\n".join(log.total_lines(ips)), flush=True)
+        if p.train_dir:
+            ckpt.save(p.train_dir, self.model, self.opt, self.global_step, self.rank)
+        summary = {"model": self.model.name, "images_per_sec": ips, "ms_per_step": 1e3 * total_s / p.num_batches,
+                   "global_batch": self.global_batch, "world": self.world, "fabric": self.fabric,
+                   "kernels": self.kernels, "final_loss": losses[-1] if losses else None}
+        if p.json_summary and self.rank == 0:
+            with open(p.json_summary, "w") as f:
+                json.dump(summary, f)
+        if self.timeline is not None:
+            self.timeline.close()
+        return summary
+
+    def _maybe_save(self):
+        p = self.p
+        if not p.train_dir or self.p.forward_only:
+            return
+        due = (p.save_model_steps and self.global_step % p.save_model_steps == 0) or \
+              (p.save_model_secs and time.time() - self._last_save >= p.save_model_secs)
+        if due:
+            ckpt.save(p.train_dir, self.model, self.opt, self.global_step, self.rank)
+            self._last_save = time.time()
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    params = flags_mod.parse(argv)
+    bench = BenchmarkCNN(params)
+    try:
+        bench.run()
+    finally:
+        if bench.use_hvd:
+            hvd.shutdown()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

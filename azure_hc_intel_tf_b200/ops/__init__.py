@@ -1,0 +1,130 @@
+"""Layer-level ops used by the model zoo.
+
+Every function takes the layer module (for its parameters and static geometry) and dispatches on
+``module.cfg.kernels``:
+
+* ``'b200'``  → ops/b200.py: hand-written sm_100a kernels from libb200cnn.so (NHWC bf16).
+* ``'cudnn'`` → stock PyTorch ops (cuDNN/cuBLAS on GPU, native kernels on CPU). This is the measured
+  baseline and the CPU plumbing path; it is never the product path on a GPU.
+
+Counterparts in the reference stack are the MKL-DNN primitives TensorFlow calls when the launcher
+passes ``--mkl=TRUE --data_format=NCHW`` (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:72,76).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+
+def _b200():
+    from . import b200
+    return b200
+
+
+def _sym(pad):
+    (pt, pb), (pl, pr) = pad
+    return pt == pb and pl == pr
+
+
+# ------------------------------------------------------------------------------------ conv block
+
+def conv_block(x, m, relu: bool):
+    """conv (+bias) (+training-mode batch-norm) (+ReLU)."""
+    if m.cfg.kernels == "b200":
+        return _b200().conv_block(x, m, relu)
+    (pt, pb), (pl, pr) = m.pad
+    if _sym(m.pad):
+        y = F.conv2d(x, m.weight, None if m.bn is not None else m.bias, m.stride, (pt, pl))
+    else:
+        y = F.conv2d(F.pad(x, (pl, pr, pt, pb)), m.weight, None if m.bn is not None else m.bias, m.stride)
+    if m.bn is not None:
+        y = batch_norm(y, m.bn, relu=relu)
+    elif relu:
+        y = F.relu(y, inplace=True)
+    return y
+
+
+def batch_norm(y, bn, relu: bool = False, residual=None):
+    """Training-mode BN; optional fused residual add and ReLU (y = relu(bn(y) + residual))."""
+    if bn.cfg.kernels == "b200":
+        return _b200().batch_norm(y, bn, relu, residual)
+    out = F.batch_norm(y, bn.moving_mean, bn.moving_variance, bn.gamma, bn.beta, bn.training,
+                       1.0 - bn.decay, bn.eps)
+    if residual is not None:
+        out = out + residual
+    if relu:
+        out = F.relu(out, inplace=True)
+    return out
+
+
+def conv_bn_add_relu(x, m, residual):
+    """Last conv of a residual block: relu(bn(conv(x)) + residual)."""
+    if m.cfg.kernels == "b200":
+        return _b200().conv_block(x, m, True, residual=residual)
+    (pt, pb), (pl, pr) = m.pad
+    y = F.conv2d(x if _sym(m.pad) else F.pad(x, (pl, pr, pt, pb)), m.weight, None, m.stride,
+                 (pt, pl) if _sym(m.pad) else 0)
+    return batch_norm(y, m.bn, relu=True, residual=residual)
+
+
+# ------------------------------------------------------------------------------------ dense / pool
+
+def affine(x, m, relu: bool):
+    if m.cfg.kernels == "b200":
+        return _b200().affine(x, m, relu)
+    y = F.linear(x, m.weight, m.bias)
+    return F.relu(y, inplace=True) if relu else y
+
+
+def pool(x, m):
+    if m.cfg.kernels == "b200":
+        return _b200().pool(x, m)
+    (pt, pb), (pl, pr) = m.pad
+    if m.kind == "max":
+        if not _sym(m.pad) or pt or pl:
+            x = F.pad(x, (pl, pr, pt, pb), value=float("-inf"))
+        return F.max_pool2d(x, m.k, m.stride)
+    # TF 'SAME' average pooling divides by the number of valid (unpadded) taps.
+    if _sym(m.pad):
+        return F.avg_pool2d(x, m.k, m.stride, (pt, pl), count_include_pad=False)
+    ones = torch.ones_like(x[:1, :1])
+    num = F.avg_pool2d(F.pad(x, (pl, pr, pt, pb)), m.k, m.stride)
+    den = F.avg_pool2d(F.pad(ones, (pl, pr, pt, pb)), m.k, m.stride)
+    return num / den
+
+
+def spatial_mean(x, cfg):
+    if cfg.kernels == "b200":
+        return _b200().spatial_mean(x)
+    return x.mean(dim=(2, 3))
+
+
+def add_relu(a, b, cfg):
+    if cfg.kernels == "b200":
+        return _b200().add_relu(a, b)
+    return F.relu(a + b, inplace=True)
+
+
+def concat_channels(xs):
+    # channels_last tensors: the concat is a strided copy into the channel-interleaved output.
+    return torch.cat(xs, dim=1)
+
+
+# ------------------------------------------------------------------------------------ loss
+
+def softmax_cross_entropy(logits, labels, cfg=None):
+    """Mean softmax cross-entropy over the batch (tf_cnn_benchmarks ``loss_function``)."""
+    if cfg is not None and cfg.kernels == "b200":
+        return _b200().softmax_cross_entropy(logits, labels)
+    return F.cross_entropy(logits.float(), labels)
+
+
+def l2_loss(params, weight_decay: float):
+    """tf_cnn_benchmarks adds ``weight_decay * sum(tf.nn.l2_loss(v))`` = wd/2·Σ‖v‖² over trainable
+    variables. Its gradient, ``wd·v``, is folded into the optimizer kernels; this function only reports
+    the scalar for the ``total_loss`` column."""
+    tot = None
+    for p in params:
+        s = p.detach().float().pow(2).sum()
+        tot = s if tot is None else tot + s
+    return 0.5 * weight_decay * tot if tot is not None else torch.zeros(())

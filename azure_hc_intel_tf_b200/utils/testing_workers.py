@@ -1,0 +1,104 @@
+"""Worker bodies for the multi-process tests (they must live in an importable module for ``spawn``)."""
+from __future__ import annotations
+
+import copy
+
+import torch
+import torch.nn as nn
+
+
+def w_basic(rank, world):
+    from .. import hvd
+    assert hvd.size() == world and hvd.rank() == rank and hvd.local_rank() == rank
+    dev = hvd.device()
+    t = torch.full((5,), float(rank + 1), device=dev)
+    s = hvd.allreduce(t, op=hvd.Sum)
+    a = hvd.allreduce(t)                       # average is the default, as in horovod.torch
+    g = hvd.allgather(torch.full((rank + 1, 2), float(rank), device=dev))
+    b = hvd.broadcast(torch.full((3,), float(rank), device=dev), root_rank=world - 1)
+    h = hvd.allreduce_async_(torch.ones(4, device=dev), op=hvd.Sum)
+    while not hvd.poll(h):
+        pass
+    z = hvd.synchronize(h)
+    obj = hvd.broadcast_object({"r": rank}, 0)
+    return (s.cpu().tolist(), a.cpu().tolist(), g.shape[0], b.cpu().tolist(), z.cpu().tolist(), obj)
+
+
+def _net(dev, kernels=None):
+    torch.manual_seed(1234)
+    net = nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.ReLU(), nn.Conv2d(8, 4, 3, padding=1), nn.Flatten(),
+                        nn.Linear(4 * 8 * 8, 10))
+    return net.to(dev).to(memory_format=torch.channels_last)
+
+
+def w_dist_opt(rank, world, mode, steps):
+    """Train a tiny BN-free net on this rank's shard; return final weights. ``mode``:
+    'fused'  — hvd.MomentumSGD wrapped by DistributedOptimizer (flat fused path)
+    'generic' — torch.optim.SGD wrapped (Horovod-over-library path)"""
+    from .. import hvd
+    dev = hvd.device()
+    net = _net(dev)
+    if rank != 0:                         # ranks start different; broadcast must fix that
+        with torch.no_grad():
+            for p in net.parameters():
+                p.add_(1.0)
+    named = list(net.named_parameters())
+    if mode == "fused":
+        base = hvd.MomentumSGD(named, lr=0.05, momentum=0.9, weight_decay=1e-3, fusion_threshold=8192)
+    elif mode == "lars":
+        base = hvd.LARS(named, lr=0.05, momentum=0.9, weight_decay=1e-3, eta=0.01, fusion_threshold=8192)
+    else:
+        base = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3)
+    opt = hvd.DistributedOptimizer(base, named_parameters=named, fusion_threshold=8192)
+    hvd.broadcast_parameters(net.state_dict(), root_rank=0)
+    hvd.broadcast_optimizer_state(opt, root_rank=0)
+    g = torch.Generator().manual_seed(7)
+    full_x = torch.randn(steps, 4 * world, 3, 8, 8, generator=g)
+    full_y = torch.randn(steps, 4 * world, 10, generator=g)
+    for s in range(steps):
+        x = full_x[s, rank * 4:(rank + 1) * 4].to(dev)
+        y = full_y[s, rank * 4:(rank + 1) * 4].to(dev)
+        opt.zero_grad()
+        ((net(x) - y) ** 2).mean().backward()
+        opt.step()
+    return [p.detach().cpu().contiguous() for p in net.parameters()], len(opt.plan.buckets)
+
+
+def single_process_reference(world, mode, steps):
+    net = _net("cpu")
+    if mode == "lars":
+        from .. import hvd
+        opt = hvd.LARS(list(net.named_parameters()), lr=0.05, momentum=0.9, weight_decay=1e-3, eta=0.01)
+    else:
+        opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3)
+    g = torch.Generator().manual_seed(7)
+    full_x = torch.randn(steps, 4 * world, 3, 8, 8, generator=g)
+    full_y = torch.randn(steps, 4 * world, 10, generator=g)
+    for s in range(steps):
+        opt.zero_grad()
+        ((net(full_x[s]) - full_y[s]) ** 2).mean().backward()
+        opt.step()
+    return [p.detach().cpu().contiguous() for p in net.parameters()]
+
+
+def w_plan_mismatch(rank, world):
+    from .. import hvd
+    dev = hvd.device()
+    net = nn.Linear(4 + rank, 3).to(dev)           # ranks disagree on the model
+    opt = hvd.DistributedOptimizer(hvd.MomentumSGD(list(net.named_parameters()), lr=0.1))
+    net(torch.randn(2, 4 + rank, device=dev)).sum().backward()
+    try:
+        opt.step()
+    except RuntimeError as e:
+        return "mismatch" if "fusion plans differ" in str(e) else str(e)
+    return "no error"
+
+
+def w_cli(rank, world, argv):
+    from ..cli import cnn_benchmarks
+    from ..utils import flags
+    p = flags.parse(argv)
+    b = cnn_benchmarks.BenchmarkCNN(p)
+    out = b.run()
+    first = next(iter(b.model.parameters())).detach().float().cpu().sum().item()
+    return out["images_per_sec"], first

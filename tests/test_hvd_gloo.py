@@ -1,0 +1,39 @@
+"""Distributed plumbing on CPU/gloo, world_size=2 — BASELINE.json configs[0]; the analogue of the
+reference's single-node multi-worker mode (run-tf-sing-ucx-openmpi.sh:100 ``--oversubscribe``) over its
+``sock`` fabric (:94)."""
+import pytest
+import torch
+
+from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
+
+
+def test_api_basics_ws2():
+    outs = testing.run_ranks(W.w_basic, 2, "gloo")
+    for r, (s, a, g, b, z, obj) in enumerate(outs):
+        assert s == [3.0] * 5 and a == [1.5] * 5 and g == 3 and b == [1.0] * 3 and z == [2.0] * 4
+        assert obj == {"r": 0}
+
+
+@pytest.mark.parametrize("mode", ["fused", "generic", "lars"])
+def test_distributed_optimizer_matches_single_process(mode):
+    steps = 4
+    outs = testing.run_ranks(W.w_dist_opt, 2, "gloo", args=(mode, steps))
+    (w0, nb0), (w1, nb1) = outs
+    assert nb0 > 1                                   # several fusion buckets were exercised
+    for a, b in zip(w0, w1):
+        assert torch.equal(a, b)                     # ranks end bit-identical
+    ref = W.single_process_reference(2, mode, steps)
+    for a, r in zip(w0, ref):
+        assert torch.allclose(a, r, atol=2e-6, rtol=1e-4)
+
+
+def test_plan_mismatch_is_detected():
+    assert testing.run_ranks(W.w_plan_mismatch, 2, "gloo") == ["mismatch", "mismatch"]
+
+
+def test_cli_resnet50_batch32_ws2_cpu():
+    # BASELINE.json configs[0]: ResNet-50, batch 32/worker, world_size=2 on CPU/gloo (plumbing, shortened)
+    argv = ["--model=resnet50", "--batch_size=32", "--num_batches=1", "--num_warmup_batches=0", "--device=cpu",
+            "--variable_update=horovod", "--display_every=1", "--optimizer=momentum"]
+    outs = testing.run_ranks(W.w_cli, 2, "gloo", args=(argv,), timeout=900)
+    assert outs[0][0] > 0 and abs(outs[0][1] - outs[1][1]) < 1e-3     # same weights on both ranks
