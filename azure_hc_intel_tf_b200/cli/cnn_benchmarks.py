@@ -71,7 +71,7 @@ class BenchmarkCNN:
                 hvd.broadcast_optimizer_state(self.opt, root_rank=0)
         src = data_mod.HostSynthetic if data_source == "host" else data_mod.DeviceSynthetic
         self.data = src(self.batch, self.model.image_size, self.model.cfg.num_classes, self.device, self.dtype,
-                        seed=p.seed + self.rank)
+                        seed=p.seed + self.rank, own_kernels=self.kernels == "b200")
         self._graph = None
         self._last_save = time.time()
 

@@ -1,0 +1,361 @@
+"""Layer ops on the hand-written sm_100a kernels (libb200cnn.so), NHWC bf16.
+
+Each public function mirrors one in ops/__init__.py. Tensors are logical-NCHW ``channels_last`` (so the
+storage is NHWC and ``data_ptr()`` can be handed to the kernels unchanged).
+
+Gradient hand-off: when a parameter's ``.grad`` is a view into a fusion buffer (the optimizer attached
+``grad_ready``), backward writes the fp32 gradient straight into that view and calls ``grad_ready()`` —
+the Horovod "enqueue tensor" moment — instead of returning it to autograd. Otherwise the gradient is
+returned normally.
+
+Counterpart in the reference stack: TensorFlow + MKL-DNN primitives under ``--mkl=TRUE``
+(benchmark-scripts/run-tf-sing-ucx-openmpi.sh:76); SURVEY.md §2.6 K1–K9.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import _native
+from .._cuda_sigs import PoolGeom
+from . import conv_impl
+
+_BF16 = torch.bfloat16
+_scratch = {}
+launch_count = 0          # kernels of ours enqueued since the last reset (bench.py reports it)
+
+
+def lib():
+    return _native.cuda()
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check(rc, name):
+    global launch_count
+    launch_count += 1
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib().b200_last_error().decode()}")
+
+
+def count_launch(n=1):
+    global launch_count
+    launch_count += n
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def scratch(device) -> torch.Tensor:
+    """Per-device reduction scratch (partials + ticket counters). Kernels using it run on one stream."""
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    s = _scratch.get(key)
+    if s is None:
+        s = torch.zeros(8 << 20, dtype=torch.uint8, device=device)
+        _scratch[key] = s
+    return s
+
+
+def nhwc(x: torch.Tensor) -> torch.Tensor:
+    """Ensure bf16 channels_last storage; returns the same logical-NCHW tensor."""
+    if x.dtype != _BF16:
+        x = x.to(_BF16)
+    if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    return x
+
+
+def empty_nhwc(n, c, h, w, device, dtype=_BF16):
+    return torch.empty((n, h, w, c), dtype=dtype, device=device).permute(0, 3, 1, 2)
+
+
+def _direct(p: Optional[torch.Tensor]):
+    """The fp32 fusion-buffer view to write this parameter's gradient into, or None."""
+    if p is not None and p.requires_grad and getattr(p, "grad_ready", None) is not None and p.grad is not None:
+        return p.grad
+    return None
+
+
+def _deliver(p, grad_view, value):
+    """Return value for autograd: None if the gradient was written in place (and signal readiness)."""
+    if grad_view is not None:
+        p.grad_ready()
+        return None
+    return value
+
+
+def lowp(p: torch.Tensor) -> torch.Tensor:
+    lp = getattr(p, "lp", None)
+    return lp if lp is not None else p.detach().to(_BF16)
+
+
+# ------------------------------------------------------------------------------------ BN pieces
+
+def bn_forward(y, bn, residual, relu):
+    """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift)."""
+    n, c, h, w = y.shape
+    rows = n * h * w
+    dev = y.device
+    stats = torch.empty((4, c), dtype=torch.float32, device=dev)
+    mean, rstd, scale, shift = stats[0], stats[1], stats[2], stats[3]
+    training = bn.training
+    if training:
+        _check(lib().b200_bn_stats(_ptr(y), rows, c, _ptr(bn.gamma), _ptr(bn.beta), _ptr(bn.moving_mean),
+                                   _ptr(bn.moving_variance), bn.decay, bn.eps, _ptr(mean), _ptr(rstd), _ptr(scale),
+                                   _ptr(shift), _ptr(scratch(dev)), _stream()), "bn_stats")
+    else:
+        rstd.copy_(torch.rsqrt(bn.moving_variance + bn.eps))
+        mean.copy_(bn.moving_mean)
+        scale.copy_(bn.gamma.detach() * rstd)
+        shift.copy_(bn.beta.detach() - mean * scale)
+    z = empty_nhwc(n, c, h, w, dev)
+    _check(lib().b200_bn_apply(_ptr(y), _ptr(residual), _ptr(z), rows, c, _ptr(scale), _ptr(shift), int(relu),
+                               _stream()), "bn_apply")
+    return z, stats
+
+
+def bn_backward(dz, y, z_for_mask, stats, relu, want_dres, dgamma_out, dbeta_out):
+    n, c, h, w = y.shape
+    rows = n * h * w
+    dev = y.device
+    mean, rstd, scale, shift = stats[0], stats[1], stats[2], stats[3]
+    dgamma = dgamma_out if dgamma_out is not None else torch.empty(c, dtype=torch.float32, device=dev)
+    dbeta = dbeta_out if dbeta_out is not None else torch.empty(c, dtype=torch.float32, device=dev)
+    _check(lib().b200_bn_bwd_reduce(_ptr(dz), _ptr(y), _ptr(z_for_mask), rows, c, _ptr(mean), _ptr(rstd), _ptr(scale),
+                                    _ptr(shift), int(relu), _ptr(dgamma), _ptr(dbeta), _ptr(scratch(dev)), _stream()),
+           "bn_bwd_reduce")
+    dy = empty_nhwc(n, c, h, w, dev)
+    dres = empty_nhwc(n, c, h, w, dev) if want_dres else None
+    _check(lib().b200_bn_bwd_apply(_ptr(dz), _ptr(y), _ptr(z_for_mask), _ptr(dy), _ptr(dres), rows, c, _ptr(mean),
+                                   _ptr(rstd), _ptr(scale), _ptr(shift), _ptr(dgamma), _ptr(dbeta), int(relu),
+                                   _stream()), "bn_bwd_apply")
+    return dy, dres, dgamma, dbeta
+
+
+# ------------------------------------------------------------------------------------ conv block
+
+class _ConvBlock(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, bias, residual, m, relu):
+        x = nhwc(x)
+        if residual is not None:
+            residual = nhwc(residual)
+        w_lp = lowp(weight)
+        y = conv_impl.fprop(x, w_lp, m)
+        ctx.m, ctx.relu = m, relu
+        ctx.has_res = residual is not None
+        if m.bn is not None:
+            z, stats = bn_forward(y, m.bn, residual, relu)
+            # the ReLU mask is recomputed from y when there is no residual, else read from z
+            ctx.save_for_backward(x, w_lp, y, z if (relu and residual is not None) else None, stats)
+        else:
+            if bias is not None or relu:
+                n, c, h, w = y.shape
+                _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
+            z = y
+            ctx.save_for_backward(x, w_lp, None, z if relu else None, None)
+        ctx.weight, ctx.gamma, ctx.beta, ctx.bias = weight, gamma, beta, bias
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        m, relu = ctx.m, ctx.relu
+        x, w_lp, y, z, stats = ctx.saved_tensors
+        weight, gamma, beta, bias = ctx.weight, ctx.gamma, ctx.beta, ctx.bias
+        dz = nhwc(dz)
+        dres = dgamma = dbeta = dbias = None
+        g_gamma = g_beta = g_bias = None
+        if m.bn is not None:
+            g_gamma = _direct(gamma) if (gamma is not None and gamma.requires_grad) else None
+            g_beta = _direct(beta)
+            dy, dres, dgamma, dbeta = bn_backward(dz, y, z, stats, relu, ctx.has_res, g_gamma, g_beta)
+        else:
+            n, c, h, w = dz.shape
+            if bias is not None:
+                g_bias = _direct(bias)
+                dbias = g_bias if g_bias is not None else torch.empty(c, dtype=torch.float32, device=dz.device)
+                dy = empty_nhwc(n, c, h, w, dz.device) if relu else dz
+                _check(lib().b200_bias_act_bwd(_ptr(dz), _ptr(z), _ptr(dy) if relu else _ptr(None), _ptr(dbias),
+                                               n * h * w, c, int(relu), _ptr(scratch(dz.device)), _stream()),
+                       "bias_act_bwd")
+            elif relu:
+                dy = torch.where(z > 0, dz, torch.zeros_like(dz))
+            else:
+                dy = dz
+        g_w = _direct(weight)
+        dw = conv_impl.wgrad(x, dy, m, out=g_w)
+        dx = conv_impl.dgrad(dy, w_lp, m, x.shape) if ctx.needs_input_grad[0] else None
+        return (dx, _deliver(weight, g_w, dw),
+                _deliver(gamma, g_gamma, dgamma) if (gamma is not None and gamma.requires_grad) else None,
+                _deliver(beta, g_beta, dbeta) if beta is not None else None,
+                _deliver(bias, g_bias, dbias) if bias is not None else None,
+                dres, None, None)
+
+
+def conv_block(x, m, relu, residual=None):
+    bn = m.bn
+    return _ConvBlock.apply(x, m.weight, bn.gamma if bn is not None else None, bn.beta if bn is not None else None,
+                            m.bias, residual, m, relu)
+
+
+def batch_norm(y, bn, relu, residual):
+    raise NotImplementedError("standalone batch_norm is only reached through conv_block on the b200 path")
+
+
+# ------------------------------------------------------------------------------------ affine
+
+class _Affine(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, m, relu):
+        x2 = x.to(_BF16).contiguous()
+        w_lp = lowp(weight)
+        y = conv_impl.gemm_nt(x2, w_lp)                     # [B, out] bf16
+        b, c = y.shape
+        if c % 8 == 0:
+            _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), b, c, int(relu), _stream()), "bias_act")
+        else:                                                # 1001-way head: tiny, unaligned
+            y = y + bias.to(y.dtype)
+            if relu:
+                y = torch.relu_(y)
+        ctx.save_for_backward(x2, w_lp, y if relu else None)
+        ctx.weight, ctx.bias, ctx.relu = weight, bias, relu
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w_lp, y = ctx.saved_tensors
+        weight, bias = ctx.weight, ctx.bias
+        dy = dy.to(_BF16).contiguous()
+        b, c = dy.shape
+        g_b = _direct(bias)
+        if c % 8 == 0:
+            dbias = g_b if g_b is not None else torch.empty(c, dtype=torch.float32, device=dy.device)
+            d2 = torch.empty_like(dy) if ctx.relu else dy
+            _check(lib().b200_bias_act_bwd(_ptr(dy), _ptr(y), _ptr(d2) if ctx.relu else _ptr(None), _ptr(dbias), b, c,
+                                           int(ctx.relu), _ptr(scratch(dy.device)), _stream()), "bias_act_bwd")
+            dy = d2
+        else:
+            if ctx.relu:
+                dy = torch.where(y > 0, dy, torch.zeros_like(dy))
+            s = dy.float().sum(0)
+            if g_b is not None:
+                g_b.copy_(s)
+            dbias = s
+        g_w = _direct(weight)
+        dw = conv_impl.gemm_tn_f32(dy, x2, out=g_w)          # [out, in] fp32
+        dx = conv_impl.gemm_nn(dy, w_lp) if ctx.needs_input_grad[0] else None
+        return dx, _deliver(weight, g_w, dw), _deliver(bias, g_b, dbias), None, None
+
+
+def affine(x, m, relu):
+    return _Affine.apply(x, m.weight, m.bias, m, relu)
+
+
+# ------------------------------------------------------------------------------------ pooling
+
+def _geom(x, m) -> PoolGeom:
+    n, c, h, w = x.shape
+    p, q = m.out_hw
+    return PoolGeom(n, h, w, c, p, q, m.k[0], m.k[1], m.stride[0], m.stride[1], m.pad[0][0], m.pad[1][0])
+
+
+class _Pool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, m):
+        x = nhwc(x)
+        g = _geom(x, m)
+        y = empty_nhwc(g.n, g.c, g.p, g.q, x.device)
+        if m.kind == "max":
+            idx = torch.empty((g.n, g.p, g.q, g.c), dtype=torch.uint8, device=x.device)
+            _check(lib().b200_maxpool_fwd(_ptr(x), _ptr(y), _ptr(idx), C.byref(g), _stream()), "maxpool_fwd")
+            ctx.save_for_backward(idx)
+        else:
+            _check(lib().b200_avgpool_fwd(_ptr(x), _ptr(y), C.byref(g), _stream()), "avgpool_fwd")
+        ctx.g, ctx.kind = g, m.kind
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        g = ctx.g
+        dy = nhwc(dy)
+        dx = empty_nhwc(g.n, g.c, g.h, g.w, dy.device)
+        if ctx.kind == "max":
+            (idx,) = ctx.saved_tensors
+            _check(lib().b200_maxpool_bwd(_ptr(dy), _ptr(idx), _ptr(dx), C.byref(g), _stream()), "maxpool_bwd")
+        else:
+            _check(lib().b200_avgpool_bwd(_ptr(dy), _ptr(dx), C.byref(g), _stream()), "avgpool_bwd")
+        return dx, None
+
+
+def pool(x, m):
+    return _Pool.apply(x, m)
+
+
+class _SpatialMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = nhwc(x)
+        n, c, h, w = x.shape
+        y = torch.empty((n, c), dtype=_BF16, device=x.device)
+        _check(lib().b200_spatial_mean_fwd(_ptr(x), _ptr(y), n, h * w, c, _stream()), "spatial_mean_fwd")
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        n, c, h, w = ctx.shape
+        dy = dy.to(_BF16).contiguous()
+        dx = empty_nhwc(n, c, h, w, dy.device)
+        _check(lib().b200_spatial_mean_bwd(_ptr(dy), _ptr(dx), n, h * w, c, _stream()), "spatial_mean_bwd")
+        return dx
+
+
+def spatial_mean(x):
+    return _SpatialMean.apply(x)
+
+
+def add_relu(a, b):
+    raise NotImplementedError("residual add is fused into conv_block(residual=...) on the b200 path")
+
+
+# ------------------------------------------------------------------------------------ loss / input
+
+class _SoftmaxXent(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels):
+        lg = logits.float().contiguous()
+        b, classes = lg.shape
+        ld_d = (classes + 7) // 8 * 8
+        rows = torch.empty(b, dtype=torch.float32, device=lg.device)
+        loss = torch.empty((), dtype=torch.float32, device=lg.device)
+        d = torch.empty((b, ld_d), dtype=_BF16, device=lg.device)
+        _check(lib().b200_softmax_xent(_ptr(lg), classes, _ptr(labels), b, classes, _ptr(rows), _ptr(loss), _ptr(d),
+                                       ld_d, 1.0, _stream()), "softmax_xent")
+        count_launch(1)
+        ctx.save_for_backward(d)
+        ctx.classes, ctx.dtype = classes, logits.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        out = d[:, :ctx.classes]
+        # g is 1.0 in training (loss.backward()); honour other scalings without a sync
+        return (out * g.to(out.dtype)).to(ctx.dtype), None
+
+
+def softmax_cross_entropy(logits, labels):
+    return _SoftmaxXent.apply(logits, labels)
+
+
+def normalize_u8(u8_nhwc: torch.Tensor, c_out: Optional[int] = None) -> torch.Tensor:
+    n, h, w, c = u8_nhwc.shape
+    c_out = c_out or c
+    y = torch.empty((n, h, w, c_out), dtype=_BF16, device=u8_nhwc.device)
+    _check(lib().b200_normalize_u8(_ptr(u8_nhwc), _ptr(y), n * h * w, c, c_out, _stream()), "normalize_u8")
+    return y.permute(0, 3, 1, 2)

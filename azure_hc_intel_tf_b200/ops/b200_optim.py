@@ -1,0 +1,25 @@
+"""GPU side of hvd.MomentumSGD: flat momentum-SGD / LARS kernels from libb200cnn.so (csrc/kernels/optim.cu).
+Reference role: TF ApplyMomentum under --optimizer=momentum (run-tf-sing-ucx-openmpi.sh:73)."""
+from __future__ import annotations
+
+from . import b200
+from .b200 import _check, _ptr, _stream, lib
+
+
+def sgd_update(opt, lo: int, hi: int, lr: float, mu: float, wd: float, grad_scale: float):
+    if hi <= lo:
+        return
+    blk = opt.block_tensor[lo // 1024:]
+    shadow = opt.shadow[lo:] if opt.shadow is not None else None
+    _check(lib().b200_sgd_momentum_flat(_ptr(opt.master[lo:]), _ptr(opt.mom[lo:]), _ptr(opt.grad[lo:]), _ptr(shadow),
+                                        hi - lo, _ptr(blk), _ptr(opt.tensor_decay), _ptr(opt.tensor_lars),
+                                        _ptr(opt.trust) if opt.lars else _ptr(None), lr, mu, wd, grad_scale,
+                                        _stream()), "sgd_momentum_flat")
+
+
+def lars_trust(opt, wd: float, grad_scale: float):
+    opt.norms.zero_()
+    _check(lib().b200_lars_norms(_ptr(opt.master), _ptr(opt.grad), opt.total, _ptr(opt.block_tensor), _ptr(opt.norms),
+                                 grad_scale, _stream()), "lars_norms")
+    _check(lib().b200_lars_trust(_ptr(opt.norms), _ptr(opt.tensor_decay), _ptr(opt.tensor_lars), _ptr(opt.trust),
+                                 len(opt.flags), opt.lars_eta, wd, opt.lars_eps, _stream()), "lars_trust")

@@ -27,7 +27,8 @@ def _truncated_normal_u8(shape, gen, mean=127.0, std=60.0):
 
 
 class DeviceSynthetic:
-    def __init__(self, batch: int, image_size: int, num_classes: int, device, dtype, seed: int = 0):
+    def __init__(self, batch: int, image_size: int, num_classes: int, device, dtype, seed: int = 0,
+                 own_kernels: bool = True):
         gen = torch.Generator().manual_seed(seed)
         u8 = _truncated_normal_u8((batch, image_size, image_size, 3), gen)
         img = (u8.float() / 127.5 - 1.0).to(dtype)
@@ -42,7 +43,9 @@ class DeviceSynthetic:
 class HostSynthetic:
     """Pinned-host uint8 source with a double-buffered async H2D copy and an on-device normalise/cast."""
 
-    def __init__(self, batch: int, image_size: int, num_classes: int, device, dtype, seed: int = 0, nbuf: int = 2):
+    def __init__(self, batch: int, image_size: int, num_classes: int, device, dtype, seed: int = 0, nbuf: int = 2,
+                 own_kernels: bool = True):
+        self.own_kernels = own_kernels
         gen = torch.Generator().manual_seed(seed)
         self.device, self.dtype = torch.device(device), dtype
         cuda = self.device.type == "cuda"
@@ -82,7 +85,7 @@ class HostSynthetic:
         if self.stream is not None:
             torch.cuda.current_stream().wait_event(self.ready[slot])
         u8, lab = self.dev_u8[slot], self.dev_lab[slot]
-        img = normalize_u8(u8, self.dtype)
+        img = normalize_u8(u8, self.dtype, self.own_kernels)
         labels = lab.clone()
         if self.stream is not None:
             ev = torch.cuda.Event()
@@ -92,12 +95,9 @@ class HostSynthetic:
         return img, labels
 
 
-def normalize_u8(u8_nhwc: torch.Tensor, dtype) -> torch.Tensor:
+def normalize_u8(u8_nhwc: torch.Tensor, dtype, own_kernels: bool = True) -> torch.Tensor:
     """uint8 NHWC → normalised ``dtype``, returned as a logical-NCHW channels_last tensor."""
-    if u8_nhwc.is_cuda:
-        from .. import _native
-        if _native.cuda_loaded() or _native.cuda_available():
-            from . import b200
-            if dtype == torch.bfloat16:
-                return b200.normalize_u8(u8_nhwc)
+    if u8_nhwc.is_cuda and own_kernels and dtype == torch.bfloat16:
+        from . import b200
+        return b200.normalize_u8(u8_nhwc)
     return (u8_nhwc.to(torch.float32) / 127.5 - 1.0).to(dtype).permute(0, 3, 1, 2)
