@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(256) normalize_u8_kernel(const uint8_t* __rest
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < pixels; p += (int64_t)gridDim.x * blockDim.x) {
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(y) + p * cout;
     for (int c = 0; c < cout; ++c) {
-      float v = c < cin ? (float)x[p * cin + c] * (1.0f / 127.5f) - 1.0f : 0.0f;
+      float v = c < cin ? (float)x[p * cin + c] / 127.5f - 1.0f : 0.0f;
       o[c] = __float2bfloat16(v);
     }
   }

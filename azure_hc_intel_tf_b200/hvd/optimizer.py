@@ -271,6 +271,7 @@ class DistributedOptimizer:
         self._handles = []
         self._launched = set()
         self._counts = [0] * len(self.params)
+        self._direct_seen = [False] * len(self.params)
         self._plan_checked = False
         self._hooks = []
         for i, p in enumerate(self.params):
@@ -281,11 +282,17 @@ class DistributedOptimizer:
     # -- plumbing
     def _make_hook(self, i):
         def hook(param):
+            # autograd may still run the accumulate node (and this hook) with an undefined gradient after a
+            # kernel wrote the gradient in place and signalled readiness itself: count that once, not twice
+            if self._direct_seen[i]:
+                self._direct_seen[i] = False
+                return
             self._on_ready(i)
         return hook
 
     def _make_direct(self, i):
         def ready():
+            self._direct_seen[i] = True
             self._on_ready(i)
         return ready
 
@@ -396,6 +403,7 @@ class DistributedOptimizer:
             self._opt.step()
         self._launched.clear()
         self._counts = [0] * len(self.params)
+        self._direct_seen = [False] * len(self.params)
         self.tracker.begin_step()
         return loss
 
