@@ -41,7 +41,16 @@ SIGS = {
     "b200_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
 }
 
-OPTIONAL = {}
+OPTIONAL = {
+    "b200_conv_supported": (i32, [C.POINTER(ConvGeom), i32]),
+    "b200_conv_fprop": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
+    "b200_conv_stats_rows": (i64, [C.POINTER(ConvGeom)]),
+    "b200_conv_dgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp]),
+    "b200_conv_wgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
+    "b200_conv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
+    "b200_gemm_nt": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp]),
+    "b200_conv_stats_reduce": (i32, [vp, i64, i32, vp, vp]),
+}
 
 
 def declare(lib):

@@ -1,0 +1,466 @@
+// conv_gemm.cu — implicit-GEMM convolution (forward, backward-data) and dense GEMM on the 5th-generation tensor
+// cores: tcgen05.mma with TMEM accumulators, operands staged by TMA (im2col mode for the activation operand), a
+// persistent warp-specialised CTA per SM.
+//
+// Role in the reference stack: MKL-DNN convolution forward / backward-data and inner-product primitives that
+// TensorFlow dispatches under --mkl=TRUE (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:76); K1, K2, K8 in SURVEY.md.
+//
+// GEMM view:  D[M, N] = A[M, K] * B[N, K]^T
+//   fprop : M = N*P*Q pixels, N = Cout,  K = R*S*Cin;  A = im2col(x)  (TMA im2col),  B = w[Cout][R*S*Cin]  (K-major)
+//   dgrad : M = N*H*W pixels, N = Cin,   K = R*S*Cout; A = im2col(dy) (TMA im2col),  B = w viewed [Cout][(r,s),Cin],
+//           read as an MN-major operand with the taps flipped - no transposed weight copy is made
+//   gemm  : A[M,K] row-major, B[N,K] row-major (both TMA tiled)
+//
+// CTA layout (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..5 = epilogue (TMEM -> registers -> bf16/fp32 -> global). Pipelines: smem ring (full/empty mbarriers)
+// between TMA and MMA; two TMEM accumulator stages (tmem_full/tmem_empty) between MMA and epilogue, so the
+// epilogue of tile i overlaps the main loop of tile i+1.
+#include "b200conv.h"
+#include "common.cuh"
+#include "conv/tensormap.h"
+#include "conv/umma.cuh"
+
+namespace b200 {
+namespace {
+
+using namespace umma;
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;                    // 64 bf16 = 128 bytes = one swizzle row
+constexpr int kMaxBlockN = 256;
+constexpr int kThreads = 192;
+constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kAccStages = 2;
+constexpr int kTmemCols = 512;
+
+struct GemmParams {
+  int M, N;               // output rows / columns
+  int block_n;            // tile width, multiple of 16, <= 256
+  int num_m_tiles, num_n_tiles, num_k_blocks;
+  int stages;             // smem ring depth
+  int a_im2col;           // 1: A through the im2col map, 0: A through a tiled 2-D map
+  int PQ, Q;              // output spatial extent, to decompose the first row of a tile into (n, p, q)
+  int stride_h, stride_w; // traversal strides
+  int base_h, base_w;     // bounding-box lower corner
+  int R, S, cchunks;      // filter taps and K/64 chunks per tap
+  int b_mn_major;         // dgrad: B is [k rows][n] with the taps flipped
+  int b_row_len;          // dgrad: elements between taps in a weight row = Cin
+  void* out;              // bf16 (or fp32 when out_fp32) [M][ldo]
+  int ldo;
+  int out_fp32;
+  // strided 1x1 dgrad: GEMM row (n,p,q) lands at (n, p*sy, q*sx) of an H x W image; the other pixels get zeros
+  int scatter, sy, sx, H, W;
+  float* col_stats;       // optional [num_m_tiles][2][N] per-tile column sums / sums of squares (BN statistics)
+};
+
+struct __align__(8) Barriers {
+  uint64_t full[8];
+  uint64_t empty[8];
+  uint64_t tmem_full[kAccStages];
+  uint64_t tmem_empty[kAccStages];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_t r[16]) {
+  uint4 v0, v1;
+  __nv_bfloat162 t;
+#define PK(a, b) (t = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b)), *reinterpret_cast<uint32_t*>(&t))
+  v0.x = PK(r[0], r[1]);
+  v0.y = PK(r[2], r[3]);
+  v0.z = PK(r[4], r[5]);
+  v0.w = PK(r[6], r[7]);
+  v1.x = PK(r[8], r[9]);
+  v1.y = PK(r[10], r[11]);
+  v1.z = PK(r[12], r[13]);
+  v1.w = PK(r[14], r[15]);
+#undef PK
+  reinterpret_cast<uint4*>(dst)[0] = v0;
+  reinterpret_cast<uint4*>(dst)[1] = v1;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128-byte swizzle atoms
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int b_bytes = p.block_n * kBlockK * 2;
+  const int stage_bytes = kABytes + b_bytes;
+  Barriers* bars = reinterpret_cast<Barriers*>(smem + (size_t)p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_a);
+    prefetch_tensormap(&map_b);
+    for (int i = 0; i < p.stages; ++i) {
+      mbar_init(&bars->full[i], 1);
+      mbar_init(&bars->empty[i], 1);
+    }
+    for (int i = 0; i < kAccStages; ++i) {
+      mbar_init(&bars->tmem_full[i], 1);
+      mbar_init(&bars->tmem_empty[i], 4);   // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================================================ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+        const int m0 = mt * kBlockM, n0 = nt * p.block_n;
+        int img = 0, ph = 0, qw = 0;
+        if (p.a_im2col) {
+          img = m0 / p.PQ;
+          int rem = m0 - img * p.PQ;
+          int pp = rem / p.Q;
+          ph = pp * p.stride_h + p.base_h;
+          qw = (rem - pp * p.Q) * p.stride_w + p.base_w;
+        }
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&bars->empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * stage_bytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
+          const int tap = kb / p.cchunks, cc = kb - tap * p.cchunks;
+          const int r = tap / p.S, s = tap - r * p.S;
+          if (p.a_im2col) {
+            tma_load_im2col_4d(sa, &map_a, &bars->full[stage], cc * kBlockK, qw, ph, img, (uint16_t)s, (uint16_t)r);
+          } else {
+            tma_load_2d(sa, &map_a, &bars->full[stage], kb * kBlockK, m0);
+          }
+          if (!p.b_mn_major) {
+            tma_load_2d(sb, &map_b, &bars->full[stage], kb * kBlockK, n0);
+          } else {
+            // weight row = one output channel (GEMM K index); columns = ((r,s), cin). Taps are flipped.
+            const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s);
+            for (int j = 0; j < p.block_n / 64; ++j)
+              tma_load_2d(sb + j * (kBlockK * 128), &map_b, &bars->full[stage], wtap * p.b_row_len + n0 + j * 64,
+                          cc * kBlockK);
+          }
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================ MMA issuer
+    const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN);
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(&bars->full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t sb = sa + kABytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = make_sdesc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = p.b_mn_major ? make_sdesc_sw128(sb + k * 2048, kBlockK * 128, 1024)
+                                             : make_sdesc_sw128(sb + k * 32, 16, 1024);
+            mma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          mma_commit(&bars->empty[stage]);                       // frees the smem slot when the MMAs have read it
+          if (kb == p.num_k_blocks - 1) mma_commit(&bars->tmem_full[acc]);
+        }
+        __syncwarp();
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++acc == kAccStages) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ================================================================ epilogue (warps 2..5)
+    const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+      const int row = mt * kBlockM + lane_group * 32 + lane;
+      const int n0 = nt * p.block_n;
+      mbar_wait(&bars->tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
+      const bool valid = row < p.M;
+      size_t orow = (size_t)row;
+      if (p.scatter && valid) {
+        const int img = row / p.PQ;
+        const int rem = row - img * p.PQ;
+        const int pp = rem / p.Q, qq = rem - pp * p.Q;
+        orow = ((size_t)img * p.H + (size_t)pp * p.sy) * p.W + (size_t)qq * p.sx;
+      }
+      for (int c = 0; c < p.block_n; c += 16) {
+        uint32_t r[16];
+        tmem_ld_x16(t_row + (uint32_t)c, r);
+        tmem_ld_wait();
+        if (p.col_stats) {
+          // per-column sum / sum of squares over this warp's 32 rows (rows past M contribute zeros: their A rows
+          // were zero-filled by TMA), via a halving butterfly: 16+8+4+2+1 shuffles per statistic
+          float s1[16], s2[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            // statistics are taken of the bf16-rounded value, i.e. of what is stored
+            float v = __bfloat162float(__float2bfloat16(__uint_as_float(r[i])));
+            s1[i] = v;
+            s2[i] = v * v;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], 16);
+            s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], 16);
+          }
+#pragma unroll
+          for (int w = 8; w >= 1; w >>= 1) {
+#pragma unroll
+            for (int i = 0; i < w; ++i) {
+              const bool up = (lane & w) != 0;
+              float a1 = up ? s1[i] : s1[i + w], b1 = up ? s1[i + w] : s1[i];
+              float a2 = up ? s2[i] : s2[i + w], b2 = up ? s2[i + w] : s2[i];
+              s1[i] = b1 + __shfl_xor_sync(0xffffffffu, a1, w);
+              s2[i] = b2 + __shfl_xor_sync(0xffffffffu, a2, w);
+            }
+          }
+          // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
+          if (lane < 16) {
+            const int col = lane;
+            float* dst = p.col_stats + ((size_t)mt * 4 + lane_group) * 2 * p.N + n0 + c + col;
+            dst[0] = s1[0];
+            dst[p.N] = s2[0];
+          }
+        }
+        if (valid && n0 + c < p.N) {
+          if (p.out_fp32) {
+            float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo + n0 + c;
+            if (n0 + c + 16 <= p.N && (p.ldo & 3) == 0) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                reinterpret_cast<uint4*>(o)[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+            } else {
+              for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __uint_as_float(r[i]);
+            }
+          } else {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + orow * p.ldo + n0 + c;
+            if (n0 + c + 16 <= p.N && (p.ldo & 7) == 0) {
+              store_row_bf16(o, r);
+              if (p.scatter) {
+                // the pixels the strided forward conv never read receive a zero gradient
+                const uint4 z = make_uint4(0, 0, 0, 0);
+                for (int dy = 0; dy < p.sy; ++dy)
+                  for (int dx = 0; dx < p.sx; ++dx) {
+                    if (dy == 0 && dx == 0) continue;
+                    __nv_bfloat16* oz = o + ((size_t)dy * p.W + dx) * p.ldo;
+                    reinterpret_cast<uint4*>(oz)[0] = z;
+                    reinterpret_cast<uint4*>(oz)[1] = z;
+                  }
+              }
+            } else {
+              for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __float2bfloat16(__uint_as_float(r[i]));
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+      if (++acc == kAccStages) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------- host side
+
+int pick_block_n(int n) {
+  if (n % 256 == 0) return 256;
+  if (n % 128 == 0) return 128;
+  if (n <= 256 && n % 16 == 0) return n;
+  for (int bn = 256; bn >= 16; bn -= 16)
+    if (n % bn == 0) return bn;
+  return ((n < 256 ? n : 256) + 15) / 16 * 16;   // tail columns are masked in the epilogue
+}
+
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStream_t st) {
+  const int stage_bytes = kABytes + p.block_n * kBlockK * 2;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + sizeof(Barriers) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_conv_supported(const b200_conv_geom* g, int op) {
+  if (!g) return 0;
+  if (g->n <= 0 || g->p <= 0 || g->q <= 0) return 0;
+  if (op == B200_CONV_FPROP) {
+    return g->c % 64 == 0 && g->k % 16 == 0 && g->r <= 15 && g->s <= 15;
+  }
+  if (op == B200_CONV_DGRAD) {
+    if (g->k % 64 != 0 || g->c % 64 != 0) return 0;
+    if (g->stride_h == 1 && g->stride_w == 1) return g->r <= 15 && g->s <= 15;
+    // strided: only 1x1 without padding (ResNet v1 down-sampling convolutions)
+    return g->r == 1 && g->s == 1 && g->pad_t == 0 && g->pad_l == 0 && g->pad_b == 0 && g->pad_r == 0 &&
+           g->p * g->stride_h == g->h && g->q * g->stride_w == g->w;
+  }
+  return 0;
+}
+
+int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
+                    void* stream) {
+  B200_CHECK_ARG(x && w && y && g, "conv_fprop: null pointer");
+  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin%%64==0, Cout%%16==0)");
+  CUtensorMap ma, mb;
+  const int upper_w = g->pad_r - (g->s - 1), upper_h = g->pad_b - (g->r - 1);
+  if (tmap_im2col_nhwc(&ma, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
+                       kBlockK, kBlockM))
+    return -1;
+  GemmParams p{};
+  p.M = g->n * g->p * g->q;
+  p.N = g->k;
+  p.block_n = pick_block_n(g->k);
+  const int kdim = g->r * g->s * g->c;
+  if (tmap_tiled_2d(&mb, w, 2, (uint64_t)kdim, (uint64_t)g->k, (uint64_t)kdim * 2, kBlockK, p.block_n, true)) return -1;
+  p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = (p.N + p.block_n - 1) / p.block_n;
+  p.cchunks = g->c / kBlockK;
+  p.num_k_blocks = g->r * g->s * p.cchunks;
+  p.a_im2col = 1;
+  p.PQ = g->p * g->q;
+  p.Q = g->q;
+  p.stride_h = g->stride_h;
+  p.stride_w = g->stride_w;
+  p.base_h = -g->pad_t;
+  p.base_w = -g->pad_l;
+  p.R = g->r;
+  p.S = g->s;
+  p.out = y;
+  p.ldo = g->k;
+  p.col_stats = col_stats;
+  return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+}
+
+int64_t b200_conv_stats_rows(const b200_conv_geom* g) {
+  if (!g) return -1;
+  const int64_t m = (int64_t)g->n * g->p * g->q;
+  return (m + kBlockM - 1) / kBlockM * 4;
+}
+
+int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream) {
+  B200_CHECK_ARG(dy && w && dx && g, "conv_dgrad: null pointer");
+  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_DGRAD), "conv_dgrad: unsupported geometry");
+  CUtensorMap ma, mb;
+  GemmParams p{};
+  const bool strided = g->stride_h != 1 || g->stride_w != 1;
+  if (!strided) {
+    // dx[n,h,w,:] = sum_{r,s} dy[n, h + pad_t - r, w + pad_l - s, :] . w[:, r, s, :]
+    const int lower_h = g->pad_t - (g->r - 1), lower_w = g->pad_l - (g->s - 1);
+    const int upper_h = lower_h + g->h - g->p, upper_w = lower_w + g->w - g->q;
+    if (tmap_im2col_nhwc(&ma, dy, g->n, g->p, g->q, g->k, lower_w, lower_h, upper_w, upper_h, 1, 1, kBlockK, kBlockM))
+      return -1;
+    p.M = g->n * g->h * g->w;
+    p.PQ = g->h * g->w;
+    p.Q = g->w;
+    p.base_h = lower_h;
+    p.base_w = lower_w;
+  } else {
+    if (tmap_im2col_nhwc(&ma, dy, g->n, g->p, g->q, g->k, 0, 0, 0, 0, 1, 1, kBlockK, kBlockM)) return -1;
+    p.M = g->n * g->p * g->q;
+    p.PQ = g->p * g->q;
+    p.Q = g->q;
+    p.scatter = 1;
+    p.sy = g->stride_h;
+    p.sx = g->stride_w;
+    p.H = g->h;
+    p.W = g->w;
+  }
+  p.stride_h = p.stride_w = 1;
+  p.N = g->c;
+  p.block_n = g->c % 256 == 0 ? 256 : (g->c % 128 == 0 ? 128 : 64);
+  const int row = g->r * g->s * g->c;
+  if (tmap_tiled_2d(&mb, w, 2, (uint64_t)row, (uint64_t)g->k, (uint64_t)row * 2, 64, kBlockK, true)) return -1;
+  p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = p.N / p.block_n;
+  p.cchunks = g->k / kBlockK;
+  p.num_k_blocks = g->r * g->s * p.cchunks;
+  p.a_im2col = 1;
+  p.R = g->r;
+  p.S = g->s;
+  p.b_mn_major = 1;
+  p.b_row_len = g->c;
+  p.out = dx;
+  p.ldo = g->c;
+  return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+}
+
+int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
+                 int32_t out_fp32, void* stream) {
+  B200_CHECK_ARG(a && b && out, "gemm_nt: null pointer");
+  B200_CHECK_ARG(m > 0 && n > 0 && k > 0 && k % 64 == 0 && ldo >= n, "gemm_nt: need k%%64==0 and ldo>=n");
+  CUtensorMap ma, mb;
+  GemmParams p{};
+  p.M = m;
+  p.N = n;
+  p.block_n = pick_block_n(n);
+  if (tmap_tiled_2d(&ma, a, 2, (uint64_t)k, (uint64_t)m, (uint64_t)k * 2, kBlockK, kBlockM, true)) return -1;
+  if (tmap_tiled_2d(&mb, b, 2, (uint64_t)k, (uint64_t)n, (uint64_t)k * 2, kBlockK, p.block_n, true)) return -1;
+  p.num_m_tiles = (m + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = (n + p.block_n - 1) / p.block_n;
+  p.cchunks = k / kBlockK;
+  p.num_k_blocks = p.cchunks;
+  p.R = p.S = 1;
+  p.out = out;
+  p.ldo = ldo;
+  p.out_fp32 = out_fp32;
+  return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,19 @@
+// tensormap.h — TMA descriptor helpers (see tensormap.cu).
+#pragma once
+
+#include <cuda.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// 2-D row-major tensor [outer][inner] of elem_bytes elements; box = box_outer rows x box_inner elements.
+int tmap_tiled_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t inner, uint64_t outer,
+                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, bool swizzle128);
+
+// im2col view of an NHWC bf16 tensor. lower/upper are the bounding-box corners of the filter's base pixel
+// (fprop: lower = -pad_lo, upper = pad_hi - (filter-1)); stride_* are the traversal strides.
+int tmap_im2col_nhwc(CUtensorMap* map, const void* base, int n, int h, int w, int c, int lower_w, int lower_h,
+                     int upper_w, int upper_h, int stride_w, int stride_h, uint32_t channels_per_pixel,
+                     uint32_t pixels_per_column);
+
+}  // namespace b200

@@ -1,19 +1,101 @@
-"""Python face of the tcgen05/TMEM/TMA implicit-GEMM convolution kernels (csrc/conv). Filled in as the
-kernels land; ``supports_*`` gate which shapes are routed here (ops/conv_impl.py)."""
+"""Python face of the tcgen05/TMEM/TMA implicit-GEMM convolution kernels (csrc/conv/conv_gemm.cu,
+conv_wgrad.cu; C ABI in include/b200conv.h). ``supports_*`` ask the library which geometries the kernels
+cover; ops/conv_impl.py routes everything else to the library fallback.
+
+Reference role: MKL-DNN convolution primitives under --mkl=TRUE (run-tf-sing-ucx-openmpi.sh:76), K1–K3."""
 from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .._cuda_sigs import ConvGeom
+from . import b200
+from .b200 import _check, _ptr, _stream, empty_nhwc, lib
+
+FPROP, DGRAD, WGRAD = 0, 1, 2
+_BF16 = torch.bfloat16
+_disabled = set(filter(None, os.environ.get("B200_CONV_DISABLE", "").split(",")))   # e.g. "wgrad,dgrad"
+
+
+def geom(x_shape, m) -> ConvGeom:
+    n, c, h, w = x_shape
+    p, q = m.out_hw
+    (pt, pb), (pl, pr) = m.pad
+    return ConvGeom(n, h, w, c, m.cout, m.k[0], m.k[1], p, q, m.stride[0], m.stride[1], pt, pl, pb, pr)
+
+
+def _ok(g, op, name) -> bool:
+    if name in _disabled:
+        return False
+    fn = getattr(lib(), "b200_conv_supported", None)
+    return bool(fn and fn(C.byref(g), op))
 
 
 def supports_fprop(x, w_lp, m) -> bool:
-    return False
+    return _ok(geom(x.shape, m), FPROP, "fprop")
 
 
 def supports_dgrad(dy, w_lp, m, x_shape) -> bool:
-    return False
+    return _ok(geom(x_shape, m), DGRAD, "dgrad")
 
 
 def supports_wgrad(x, dy, m) -> bool:
-    return False
+    return hasattr(lib(), "b200_conv_wgrad") and _ok(geom(x.shape, m), WGRAD, "wgrad")
 
 
 def supports_gemm(m_, n_, k_) -> bool:
-    return False
+    return "gemm" not in _disabled and k_ % 64 == 0 and hasattr(lib(), "b200_gemm_nt")
+
+
+def fprop(x, w_lp, m, want_stats: bool = False):
+    g = geom(x.shape, m)
+    y = empty_nhwc(g.n, g.k, g.p, g.q, x.device)
+    stats = None
+    if want_stats:
+        rows = lib().b200_conv_stats_rows(C.byref(g))
+        stats = torch.empty((rows, 2, g.k), dtype=torch.float32, device=x.device)
+    _check(lib().b200_conv_fprop(_ptr(x), _ptr(w_lp), _ptr(y), C.byref(g), _ptr(stats), _stream()), "conv_fprop")
+    return (y, stats) if want_stats else y
+
+
+def stats_reduce(stats):
+    rows, _, k = stats.shape
+    sums = torch.empty((2, k), dtype=torch.float32, device=stats.device)
+    _check(lib().b200_conv_stats_reduce(_ptr(stats), rows, k, _ptr(sums), _stream()), "conv_stats_reduce")
+    return sums
+
+
+def dgrad(dy, w_lp, m, x_shape):
+    g = geom(x_shape, m)
+    dx = empty_nhwc(g.n, g.c, g.h, g.w, dy.device)
+    _check(lib().b200_conv_dgrad(_ptr(dy), _ptr(w_lp), _ptr(dx), C.byref(g), _stream()), "conv_dgrad")
+    return dx
+
+
+_ws = {}
+
+
+def wgrad(x, dy, m, out=None):
+    g = geom(x.shape, m)
+    if out is None:
+        out = torch.empty((g.k, g.r, g.s, g.c), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+    need = lib().b200_conv_wgrad_workspace_bytes(C.byref(g))
+    ws = None
+    if need > 0:
+        key = x.device.index
+        ws = _ws.get(key)
+        if ws is None or ws.numel() < need:
+            ws = torch.empty(max(need, 64 << 20), dtype=torch.uint8, device=x.device)
+            _ws[key] = ws
+    _check(lib().b200_conv_wgrad(_ptr(x), _ptr(dy), _ptr(out), C.byref(g), _ptr(ws), _stream()), "conv_wgrad")
+    return out
+
+
+def gemm_nt(a, b, out_fp32: bool = False):
+    mm, kk = a.shape
+    nn = b.shape[0]
+    out = torch.empty((mm, nn), dtype=torch.float32 if out_fp32 else _BF16, device=a.device)
+    _check(lib().b200_gemm_nt(_ptr(a), _ptr(b), _ptr(out), mm, nn, kk, nn, int(out_fp32), _stream()), "gemm_nt")
+    return out

@@ -1,0 +1,60 @@
+/*
+ * b200conv.h — C ABI of the tcgen05/TMEM/TMA implicit-GEMM convolution and GEMM kernels in libb200cnn.so.
+ *
+ * Layouts: activations NHWC bf16; filters KRSC bf16 (PyTorch [K,C,R,S] in channels_last memory format);
+ * filter gradients KRSC fp32. All functions only enqueue work on `stream` (a cudaStream_t) and return 0 on
+ * success. Reference counterparts: MKL-DNN convolution forward / backward-data / backward-weights and
+ * inner-product under --mkl=TRUE (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:76); K1-K3, K8 in SURVEY.md.
+ */
+#ifndef B200CONV_H_
+#define B200CONV_H_
+
+#include <stdint.h>
+
+#include "b200cnn.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_conv_geom {
+  int32_t n, h, w, c;          /* input  N,H,W,Cin  */
+  int32_t k, r, s;             /* filter Cout,R,S   */
+  int32_t p, q;                /* output spatial    */
+  int32_t stride_h, stride_w;
+  int32_t pad_t, pad_l, pad_b, pad_r;
+} b200_conv_geom;
+
+enum { B200_CONV_FPROP = 0, B200_CONV_DGRAD = 1, B200_CONV_WGRAD = 2 };
+
+/* 1 if the tensor-core kernel covers this geometry for `op`, else 0 (callers fall back to a library). */
+int b200_conv_supported(const b200_conv_geom* g, int op);
+
+/* y[n,p,q,k] = sum_{r,s,c} x[n, p*sh - pad_t + r, q*sw - pad_l + s, c] * w[k,r,s,c].
+ * col_stats (optional): [b200_conv_stats_rows(g)][2][k] fp32 partial column sums and sums of squares of the
+ * stored (bf16-rounded) outputs, one row per 32 output rows group — the batch-norm statistics, produced by the
+ * epilogue so that y is not read again. */
+int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
+                    void* stream);
+int64_t b200_conv_stats_rows(const b200_conv_geom* g);
+
+/* dx = gradient of fprop wrt x. Stride 1 (any filter), or strided 1x1 without padding. */
+int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);
+
+/* dw[k,r,s,c] (fp32) = sum over pixels of dy[.,k] * x[window]. dw is overwritten. `workspace` must hold
+ * b200_conv_wgrad_workspace_bytes(g) bytes (may be NULL when that is 0). */
+int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
+                    void* stream);
+int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
+
+/* out[m, n] = a[m, k] . b[n, k]^T ; a, b row-major bf16, k % 64 == 0; out bf16 or fp32 with leading dimension ldo. */
+int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
+                 int32_t out_fp32, void* stream);
+
+/* Reduce the per-group partials written by b200_conv_fprop into sums[0..k) = Σy, sums[k..2k) = Σy². */
+int b200_conv_stats_reduce(const float* col_stats, int64_t rows, int32_t k, float* sums, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CONV_H_ */

@@ -1,0 +1,106 @@
+"""tcgen05 implicit-GEMM convolution / GEMM kernels vs F.conv2d / matmul in fp32 from the same bf16 inputs
+(K1–K3, K8)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+class M:
+    def __init__(self, cin, cout, k, stride, pad, in_hw):
+        self.cin, self.cout = cin, cout
+        self.k, self.stride = (k, k) if isinstance(k, int) else k, (stride, stride)
+        self.pad = pad
+        h, w = in_hw
+        self.out_hw = ((h + sum(pad[0]) - self.k[0]) // stride + 1, (w + sum(pad[1]) - self.k[1]) // stride + 1)
+
+    def extra_repr(self):
+        return f"{self.cin}->{self.cout} k={self.k} s={self.stride} pad={self.pad}"
+
+
+def rnd(shape_nhwc, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    n, h, w, c = shape_nhwc
+    return (torch.randn(n, h, w, c, generator=g) * scale).to(DEV).to(torch.bfloat16).permute(0, 3, 1, 2)
+
+
+def wrnd(k, c, r, s, seed):
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(k, r, s, c, generator=g) * (1.0 / (c * r * s) ** 0.5)
+    return w.to(DEV).to(torch.bfloat16).permute(0, 3, 1, 2)      # [K,C,R,S] logical, KRSC storage
+
+
+def ref_conv(x, w, m):
+    (pt, pb), (pl, pr) = m.pad
+    return F.conv2d(F.pad(x.float(), (pl, pr, pt, pb)), w.float(), None, m.stride)
+
+
+def rel_err(a, b):
+    return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+
+CASES = [
+    # (n, h, w, cin, cout, k, stride, pad)
+    (2, 56, 56, 64, 64, 1, 1, ((0, 0), (0, 0))),
+    (2, 56, 56, 64, 256, 1, 1, ((0, 0), (0, 0))),
+    (3, 56, 56, 64, 64, 3, 1, ((1, 1), (1, 1))),
+    (2, 28, 28, 128, 128, 3, 1, ((1, 1), (1, 1))),
+    (2, 14, 14, 256, 256, 3, 1, ((1, 1), (1, 1))),
+    (5, 7, 7, 512, 512, 3, 1, ((1, 1), (1, 1))),
+    (2, 56, 56, 256, 128, 1, 2, ((0, 0), (0, 0))),
+    (2, 56, 56, 256, 512, 1, 2, ((0, 0), (0, 0))),
+    (3, 7, 7, 512, 2048, 1, 1, ((0, 0), (0, 0))),
+    (2, 28, 28, 128, 128, 3, 2, ((1, 1), (1, 1))),      # ResNet v1.5 strided 3x3
+    (2, 17, 17, 128, 192, (1, 7), 1, ((0, 0), (3, 3))),  # Inception 1x7
+    (2, 17, 17, 128, 192, (7, 1), 1, ((3, 3), (0, 0))),
+    (2, 35, 35, 64, 96, 3, 1, ((1, 1), (1, 1))),
+    (2, 224, 224, 64, 64, 3, 1, ((1, 1), (1, 1))),      # VGG conv1_2
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad", CASES)
+def test_fprop(n, h, w, cin, cout, k, stride, pad):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    m = M(cin, cout, k, stride, pad, (h, w))
+    x, wt = rnd((n, h, w, cin), 1), wrnd(cout, cin, m.k[0], m.k[1], 2)
+    assert conv_umma.supports_fprop(x, wt, m)
+    y, stats = conv_umma.fprop(x, wt, m, want_stats=True)
+    torch.cuda.synchronize()
+    ref = ref_conv(x, wt, m)
+    assert y.shape == ref.shape
+    assert rel_err(y, ref) < 1e-2
+    sums = conv_umma.stats_reduce(stats)
+    yf = y.float()
+    assert torch.allclose(sums[0], yf.sum((0, 2, 3)), rtol=1e-3, atol=1e-2 * yf.abs().sum((0, 2, 3)).max().item() / 100)
+    assert torch.allclose(sums[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad", [c for c in CASES if c[4] % 64 == 0])
+def test_dgrad(n, h, w, cin, cout, k, stride, pad):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    m = M(cin, cout, k, stride, pad, (h, w))
+    x, wt = rnd((n, h, w, cin), 1), wrnd(cout, cin, m.k[0], m.k[1], 2)
+    dy = rnd((n, m.out_hw[0], m.out_hw[1], cout), 3)
+    if not conv_umma.supports_dgrad(dy, wt, m, x.shape):
+        pytest.skip("geometry not covered by the tensor-core dgrad (library fallback is used)")
+    dx = conv_umma.dgrad(dy, wt, m, x.shape)
+    torch.cuda.synchronize()
+    xf = x.float().requires_grad_()
+    ref_conv(xf, wt, m).backward(dy.float())
+    assert rel_err(dx, xf.grad) < 1e-2
+
+
+@pytest.mark.parametrize("mm,nn,kk", [(256, 1001, 2048), (64, 4096, 25088), (256, 4096, 4096), (100, 16, 64)])
+def test_gemm_nt(mm, nn, kk):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    g = torch.Generator().manual_seed(0)
+    a = (torch.randn(mm, kk, generator=g)).to(DEV).to(torch.bfloat16)
+    b = (torch.randn(nn, kk, generator=g) / kk ** 0.5).to(DEV).to(torch.bfloat16)
+    out = conv_umma.gemm_nt(a, b, out_fp32=True)
+    torch.cuda.synchronize()
+    ref = a.float() @ b.float().t()
+    assert rel_err(out, ref) < 2e-3
+    out16 = conv_umma.gemm_nt(a, b)
+    assert rel_err(out16, ref) < 1e-2
