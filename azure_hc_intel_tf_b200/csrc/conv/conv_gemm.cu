@@ -336,11 +336,14 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
 
 using namespace b200;
 
+extern "C" int b200_conv_wgrad_supported(const b200_conv_geom* g);
+
 extern "C" {
 
 int b200_conv_supported(const b200_conv_geom* g, int op) {
   if (!g) return 0;
   if (g->n <= 0 || g->p <= 0 || g->q <= 0) return 0;
+  if (op == B200_CONV_WGRAD) return b200_conv_wgrad_supported(g);
   if (op == B200_CONV_FPROP) {
     return g->c % 64 == 0 && g->k % 16 == 0 && g->r <= 15 && g->s <= 15;
   }
@@ -438,6 +441,31 @@ int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, cons
   p.b_row_len = g->c;
   p.out = dx;
   p.ldo = g->c;
+  return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+}
+
+int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16* out, int32_t m, int32_t n, int32_t k,
+                 void* stream) {
+  // out[m,n] = a[m,k] . b[k,n]; a row-major with leading dimension lda (>= k, zero padded past k is fine),
+  // b row-major [k][n] read as an MN-major operand; n % 64 == 0.
+  B200_CHECK_ARG(a && b && out, "gemm_nn: null pointer");
+  B200_CHECK_ARG(m > 0 && k > 0 && n > 0 && n % 64 == 0 && lda % 8 == 0 && lda >= k, "gemm_nn: need n%%64==0, lda%%8==0");
+  CUtensorMap ma, mb;
+  GemmParams p{};
+  p.M = m;
+  p.N = n;
+  p.block_n = n % 256 == 0 ? 256 : (n % 128 == 0 ? 128 : 64);
+  if (tmap_tiled_2d(&ma, a, 2, (uint64_t)lda, (uint64_t)m, (uint64_t)lda * 2, kBlockK, kBlockM, true)) return -1;
+  if (tmap_tiled_2d(&mb, b, 2, (uint64_t)n, (uint64_t)k, (uint64_t)n * 2, 64, kBlockK, true)) return -1;
+  p.num_m_tiles = (m + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = n / p.block_n;
+  p.cchunks = (k + kBlockK - 1) / kBlockK;
+  p.num_k_blocks = p.cchunks;
+  p.R = p.S = 1;
+  p.b_mn_major = 1;
+  p.b_row_len = n;
+  p.out = out;
+  p.ldo = n;
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 

@@ -1,0 +1,315 @@
+// conv_wgrad.cu — convolution backward-weights (and dense-layer weight gradient) on tcgen05 tensor cores.
+//
+// Role in the reference stack: MKL-DNN convolution backward-weights (K3 in SURVEY.md §2.6); its output is the
+// gradient tensor Horovod enqueues for the fused allreduce, so this kernel writes fp32 straight into the
+// fusion-buffer view of the parameter's gradient (KRSC layout).
+//
+// GEMM view (the reduction runs over output pixels):
+//     D[(tap, c), k] = sum_pix  X_im2col[pix, (tap, c)] * dY[pix, k]
+//   A = im2col(x): one TMA im2col box = 64 pixels x 64 channels of one filter tap  -> MN-major A operand
+//   B = dy       : one TMA tiled  box = 64 pixels x 64 output channels            -> MN-major B operand
+// Both operands are MN-major (the 128-byte swizzled row holds 64 M/N elements, rows are K = pixels), which is
+// exactly how NHWC activations sit in memory, so no transposed copies are made.
+//
+// Work split: a CTA owns a slice of the pixel range and a group of up to T M-tiles (128 (tap,c) rows each) times
+// one N-tile (<= 256 output channels); T*N <= 512 TMEM columns hold all its fp32 accumulators. Partial sums of the
+// pixel slices are combined with red.global.add.f32 into dw (zeroed first when more than one slice exists), or
+// stored directly when a single slice covers all pixels. Stores are coalesced: a warp's 32 lanes are 32
+// consecutive (tap,c) positions of one output channel.
+#include "b200conv.h"
+#include "common.cuh"
+#include "conv/tensormap.h"
+#include "conv/umma.cuh"
+
+namespace b200 {
+namespace {
+
+using namespace umma;
+
+constexpr int kThreads = 192;
+constexpr int kBlockK = 64;          // pixels per pipeline stage
+constexpr int kBox = 64 * 128;       // one 64 x 64 bf16 TMA box, bytes
+constexpr int kTmemCols = 512;
+constexpr int kMaxStages = 6;
+
+struct WgradParams {
+  int rows_total;        // R*S*C  (valid (tap,c) rows)
+  int C, S, RS;
+  int kout;              // output channels
+  int block_n;           // N tile (multiple of 16, <= 256)
+  int n_tiles;           // ceil(kout / block_n)
+  int m_tiles_total;     // ceil(rows_total / 128)
+  int T;                 // M tiles per CTA
+  int m_groups;          // ceil(m_tiles_total / T)
+  int slices;            // pixel slices
+  int64_t pix_total;
+  int kblocks_total;     // ceil(pix_total / 64)
+  int kblocks_per_slice;
+  int PQ, Q, stride_h, stride_w, base_h, base_w;
+  int stages;
+  int atomic;            // 1: red.add into dw, 0: plain stores
+  float* dw;
+};
+
+struct __align__(8) WBarriers {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
+                  const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int nb = (p.block_n + 63) / 64;                 // dy boxes per stage
+  const int a_bytes = p.T * 2 * kBox;
+  const int stage_bytes = a_bytes + nb * kBox;
+  WBarriers* bars = reinterpret_cast<WBarriers*>(smem + (size_t)p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // blockIdx -> (slice, n tile, m group); groups of one slice are adjacent so they share dy / x through L2
+  const int per_slice = p.m_groups * p.n_tiles;
+  const int slice = blockIdx.x / per_slice;
+  const int rem = blockIdx.x - slice * per_slice;
+  const int nt = rem / p.m_groups, mg = rem - nt * p.m_groups;
+  const int n0 = nt * p.block_n;
+  const int tile0 = mg * p.T;
+  int tiles_here = p.m_tiles_total - tile0;
+  if (tiles_here > p.T) tiles_here = p.T;
+  const int kb0 = slice * p.kblocks_per_slice;
+  int kb1 = kb0 + p.kblocks_per_slice;
+  if (kb1 > p.kblocks_total) kb1 = p.kblocks_total;
+  const int nkb = kb1 - kb0;        // >= 1 by construction
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_x);
+    prefetch_tensormap(&map_dy);
+    for (int i = 0; i < p.stages; ++i) {
+      mbar_init(&bars->full[i], 1);
+      mbar_init(&bars->empty[i], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = (uint32_t)(tiles_here * 2 * kBox + nb * kBox);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&bars->empty[stage], phase ^ 1);
+        uint8_t* sa = smem + (size_t)stage * stage_bytes;
+        uint8_t* sb = sa + a_bytes;
+        mbar_expect_tx(&bars->full[stage], tx_bytes);
+        const int64_t pix = (int64_t)kb * kBlockK;
+        const int img = (int)(pix / p.PQ);
+        const int r2 = (int)(pix - (int64_t)img * p.PQ);
+        const int pp = r2 / p.Q, qq = r2 - pp * p.Q;
+        const int hh = pp * p.stride_h + p.base_h, ww = qq * p.stride_w + p.base_w;
+        for (int t = 0; t < tiles_here; ++t) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            int idx = (tile0 + t) * 128 + half * 64;      // first (tap,c) row of this 64-row chunk
+            int tap = idx / p.C;
+            int c0 = idx - tap * p.C;
+            if (tap >= p.RS) {                            // past the last tap: load something valid, it is masked
+              tap = p.RS - 1;
+              c0 = p.C;                                   // fully out of bounds in C -> zero fill
+            }
+            const int fr = tap / p.S, fs = tap - fr * p.S;
+            tma_load_im2col_4d(sa + (t * 2 + half) * kBox, &map_x, &bars->full[stage], c0, ww, hh, img, (uint16_t)fs,
+                               (uint16_t)fr);
+          }
+        }
+        for (int j = 0; j < nb; ++j)
+          tma_load_2d(sb + j * kBox, &map_dy, &bars->full[stage], n0 + j * 64, (int32_t)pix);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(&bars->full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t sb = sa + a_bytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          const uint64_t db = make_sdesc_sw128(sb + k * 2048, kBox, 1024);
+          for (int t = 0; t < tiles_here; ++t) {
+            const uint64_t da = make_sdesc_sw128(sa + t * 2 * kBox + k * 2048, kBox, 1024);
+            mma_bf16(tmem_base + (uint32_t)(t * p.block_n), da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+        }
+        mma_commit(&bars->empty[stage]);
+        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  } else {
+    const int lane_group = warp & 3;
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+    const size_t ld = (size_t)p.rows_total;       // dw[k][rows_total]
+    for (int t = 0; t < tiles_here; ++t) {
+      const int idx = (tile0 + t) * 128 + lane_group * 32 + lane;
+      const bool valid = idx < p.rows_total;
+      const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(t * p.block_n);
+      for (int c = 0; c < p.block_n; c += 16) {
+        uint32_t r[16];
+        tmem_ld_x16(t_row + (uint32_t)c, r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int ko = n0 + c + j;
+            if (ko < p.kout) {
+              float* dst = p.dw + (size_t)ko * ld + idx;
+              if (p.atomic)
+                asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dst), "f"(__uint_as_float(r[j])) : "memory");
+              else
+                *dst = __uint_as_float(r[j]);
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+int plan(const b200_conv_geom* g, WgradParams& p) {
+  p.C = g->c;
+  p.S = g->s;
+  p.RS = g->r * g->s;
+  p.rows_total = p.RS * g->c;
+  p.kout = g->k;
+  p.block_n = g->k >= 256 ? 256 : (g->k + 15) / 16 * 16;
+  p.n_tiles = (g->k + p.block_n - 1) / p.block_n;
+  p.m_tiles_total = (p.rows_total + 127) / 128;
+  const int nb = (p.block_n + 63) / 64;
+  int T = kTmemCols / p.block_n;
+  // two pipeline stages must fit in ~200 KiB: (T*16 KiB + nb*8 KiB) * 2
+  while (T > 1 && (T * 2 * kBox + nb * kBox) * 2 > 200 * 1024) --T;
+  if (T > p.m_tiles_total) T = p.m_tiles_total;
+  p.T = T;
+  p.m_groups = (p.m_tiles_total + T - 1) / T;
+  p.pix_total = (int64_t)g->n * g->p * g->q;
+  p.kblocks_total = (int)((p.pix_total + kBlockK - 1) / kBlockK);
+  const int groups = p.m_groups * p.n_tiles;
+  int slices = (2 * kNumSMs + groups - 1) / groups;
+  int max_slices = p.kblocks_total / 4;
+  if (max_slices < 1) max_slices = 1;
+  if (slices > max_slices) slices = max_slices;
+  if (slices < 1) slices = 1;
+  p.kblocks_per_slice = (p.kblocks_total + slices - 1) / slices;
+  p.slices = (p.kblocks_total + p.kblocks_per_slice - 1) / p.kblocks_per_slice;
+  p.atomic = p.slices > 1;
+  const int stage_bytes = T * 2 * kBox + nb * kBox;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  p.PQ = g->p * g->q;
+  p.Q = g->q;
+  p.stride_h = g->stride_h;
+  p.stride_w = g->stride_w;
+  p.base_h = -g->pad_t;
+  p.base_w = -g->pad_l;
+  return 0;
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_conv_wgrad_supported(const b200_conv_geom* g) {
+  if (!g) return 0;
+  return g->c % 64 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0;
+}
+
+int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g) {
+  (void)g;
+  return 0;   // partial sums are combined with red.global.add.f32 directly in dw
+}
+
+static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
+                      void* stream);
+
+int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
+                    void* stream) {
+  (void)workspace;
+  B200_CHECK_ARG(g, "conv_wgrad: null geometry");
+  return wgrad_impl(x, dy, dw, g, g->k, stream);
+}
+
+int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t batch, int32_t in_features,
+                     int32_t out_features, int32_t dy_ld, void* stream) {
+  B200_CHECK_ARG(dy_ld >= out_features && dy_ld % 8 == 0, "dense_wgrad: dy_ld must be >= out and a multiple of 8");
+  b200_conv_geom g{};
+  g.n = batch;
+  g.h = g.w = g.p = g.q = 1;
+  g.c = in_features;
+  g.k = out_features;
+  g.r = g.s = 1;
+  g.stride_h = g.stride_w = 1;
+  return wgrad_impl(x, dy, dw, &g, dy_ld, stream);
+}
+
+static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
+                      void* stream) {
+  B200_CHECK_ARG(x && dy && dw && g, "conv_wgrad: null pointer");
+  B200_CHECK_ARG(g->c % 64 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
+                 "conv_wgrad: unsupported geometry (need Cin%%64==0, dy row stride %%8==0)");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  WgradParams p{};
+  plan(g, p);
+  p.dw = dw;
+  CUtensorMap mx, mdy;
+  const int upper_w = g->pad_r - (g->s - 1), upper_h = g->pad_b - (g->r - 1);
+  if (tmap_im2col_nhwc(&mx, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
+                       64, kBlockK))
+    return -1;
+  if (tmap_tiled_2d(&mdy, dy, 2, (uint64_t)dy_ld, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, 64, kBlockK, true)) return -1;
+  if (p.atomic) B200_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)g->k * p.rows_total, st));
+  const int nb = (p.block_n + 63) / 64;
+  const size_t smem = (size_t)p.stages * (p.T * 2 * kBox + nb * kBox) + sizeof(WBarriers) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const int grid = p.slices * p.m_groups * p.n_tiles;
+  conv_wgrad_kernel<<<grid, kThreads, smem, st>>>(mx, mdy, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -59,6 +59,7 @@ class Conv(nn.Module):
         self.k, self.stride = _pair(k), _pair(stride)
         self.activation = activation
         self.scope = scope
+        self.in_hw = tuple(in_hw)
         kh, kw = self.k
         sh, sw = self.stride
         if mode == "SAME":

