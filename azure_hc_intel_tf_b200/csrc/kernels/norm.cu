@@ -431,3 +431,64 @@ int b200_cast_f32_bf16(const float* x, b200_bf16* y, int64_t n, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200_bn_stats.
+//
+// Some callers are not allowed to obtain device memory: code running inside a framework's memory-planned region
+// (every buffer was sized and placed ahead of time), plug-ins that are handed fixed input/output buffers and nothing
+// else, or hosts whose allocator must not be re-entered from where this library is called. For them the reduction
+// scratch lives in the library image itself: one fixed array per GPU, present from the moment the library is loaded
+// on that GPU until the process exits.
+namespace b200 {
+namespace {
+
+constexpr size_t kStaticScratchBytes = 2u << 20;   // 2 MiB per GPU that loads the library
+static __device__ __align__(256) unsigned char g_bn_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+
+// Resolves the device address of the array for the current device. In host code `g_bn_static_scratch` is only a
+// handle for the runtime; the address a kernel can use has to be asked for, per device, with that device current.
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "bn_stats_noalloc: device index %d out of range", dev);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_bn_static_scratch));
+    g_static_scratch_ptr[dev] = p;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" {
+
+int64_t b200_bn_stats_noalloc_max_bytes(void) { return (int64_t)b200::kStaticScratchBytes; }
+
+int b200_bn_stats_noalloc(const b200_bf16* x, int64_t rows, int32_t c, const float* gamma, const float* beta,
+                          float* running_mean, float* running_var, float decay, float eps, float* mean, float* rstd,
+                          float* scale, float* shift, void* stream) {
+  B200_CHECK_ARG(x && mean && rstd && scale && shift, "bn_stats_noalloc: null pointer");
+  B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_stats_noalloc: need rows>0 and c%%8==0 (c=%d)", c);
+  const int64_t need = b200_bn_stats_scratch_bytes(rows, c);
+  B200_CHECK_ARG(need > 0 && (size_t)need <= kStaticScratchBytes,
+                 "bn_stats_noalloc: rows=%lld c=%d needs %lld bytes of scratch, the built-in array holds %lld; use "
+                 "b200_bn_stats with caller-provided scratch for this size",
+                 (long long)rows, c, (long long)need, (long long)kStaticScratchBytes);
+  void* scratch = nullptr;
+  if (int e = static_scratch_for_current_device(&scratch)) return e;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array keeps whatever the previous call (or an aborted one) left behind. Only the ticket counters at its
+  // head have to start at zero; the partial sums behind them are fully overwritten before they are read.
+  B200_CUDA(cudaMemsetAsync(scratch, 0, kScratchHeader * sizeof(float), st));
+  StatsPolicy pol{x, gamma, beta, running_mean, running_var, decay, eps, mean, rstd, scale, shift, rows, c};
+  return launch_col_reduce(pol, rows, c, scratch, st);
+}
+
+}  // extern "C"

@@ -59,6 +59,23 @@ int b200_bn_stats(const b200_bf16* x, int64_t rows, int32_t c, const float* gamm
                   float* running_mean, float* running_var, float decay, float eps, float* mean, float* rstd,
                   float* scale, float* shift, void* scratch, void* stream);
 
+/* b200_bn_stats for callers that cannot allocate device memory (memory-planned regions of a host framework,
+ * plug-ins given fixed buffers only, call sites where the host allocator must not be re-entered): the scratch is a
+ * fixed 2 MiB array inside the library image (b200_bn_stats_noalloc_max_bytes()), held by every GPU that loads the
+ * library until the process exits. Same inputs, outputs and results as b200_bn_stats, minus the scratch argument.
+ * This entry point has no counterpart in the reference.
+ *  - Sizes whose scratch need (b200_bn_stats_scratch_bytes) exceeds the array are rejected with -1 and a message in
+ *    b200_last_error(): 2 MiB covers any row count up to c = 512 and larger c when rows are few.
+ *  - The first call on each device looks up the array's device address (with that device current); make that
+ *    first call before starting any stream capture.
+ *  - All calls on a device share the one array: two calls that may run on the GPU at the same time (different
+ *    streams, or different threads without ordering) race. Order them on one stream or with events.
+ *  - It performs no cudaMalloc/cudaFree and calls no allocating library routine. */
+int b200_bn_stats_noalloc(const b200_bf16* x, int64_t rows, int32_t c, const float* gamma, const float* beta,
+                          float* running_mean, float* running_var, float decay, float eps, float* mean, float* rstd,
+                          float* scale, float* shift, void* stream);
+int64_t b200_bn_stats_noalloc_max_bytes(void);
+
 /* Same finalisation, but from per-channel sums already produced by a convolution epilogue:
  * sums[0..c) = Σx, sums[c..2c) = Σx². */
 int b200_bn_finalize(const float* sums, int64_t rows, int32_t c, const float* gamma, const float* beta,
