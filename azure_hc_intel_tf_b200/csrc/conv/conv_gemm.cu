@@ -50,8 +50,12 @@ struct GemmParams {
   int out_fp32;
   // strided 1x1 dgrad: GEMM row (n,p,q) lands at (n, p*sy, q*sx) of an H x W image; the other pixels get zeros
   int scatter, sy, sx, H, W;
-  float* col_stats;       // optional [num_m_tiles][2][N] per-tile column sums / sums of squares (BN statistics)
+  float* col_stats;       // optional [num_m_tiles*4][2][N] per-32-row-group column sums / sums of squares (BN statistics)
+  int tma_store;          // epilogue stages bf16 tiles in shared memory and writes them with TMA bulk stores
 };
+
+constexpr int kStageOutBytes = kBlockM * 64 * 2;   // one 128 x 64 bf16 output box, 128-byte swizzled
+constexpr int kOutBufs = 2;
 
 struct __align__(8) Barriers {
   uint64_t full[8];
@@ -80,13 +84,14 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 const GemmParams p) {
+                 const __grid_constant__ CUtensorMap map_out, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int b_bytes = p.block_n * kBlockK * 2;
   const int stage_bytes = kABytes + b_bytes;
-  Barriers* bars = reinterpret_cast<Barriers*>(smem + (size_t)p.stages * stage_bytes);
+  uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;      // kOutBufs x 16 KiB when tma_store
+  Barriers* bars = reinterpret_cast<Barriers*>(out_stage + (p.tma_store ? kOutBufs * kStageOutBytes : 0));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -95,6 +100,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_a);
     prefetch_tensormap(&map_b);
+    if (p.tma_store) prefetch_tensormap(&map_out);
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&bars->full[i], 1);
       mbar_init(&bars->empty[i], 1);
@@ -198,97 +204,174 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
-      const int row = mt * kBlockM + lane_group * 32 + lane;
-      const int n0 = nt * p.block_n;
-      mbar_wait(&bars->tmem_full[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
-      const bool valid = row < p.M;
-      size_t orow = (size_t)row;
-      if (p.scatter && valid) {
-        const int img = row / p.PQ;
-        const int rem = row - img * p.PQ;
-        const int pp = rem / p.Q, qq = rem - pp * p.Q;
-        orow = ((size_t)img * p.H + (size_t)pp * p.sy) * p.W + (size_t)qq * p.sx;
-      }
-      for (int c = 0; c < p.block_n; c += 16) {
-        uint32_t r[16];
-        tmem_ld_x16(t_row + (uint32_t)c, r);
-        tmem_ld_wait();
-        if (p.col_stats) {
-          // per-column sum / sum of squares over this warp's 32 rows (rows past M contribute zeros: their A rows
-          // were zero-filled by TMA), via a halving butterfly: 16+8+4+2+1 shuffles per statistic
-          float s1[16], s2[16];
+    if (p.tma_store) {
+      // ---- staged path: TMEM -> registers -> bf16 -> swizzled shared memory -> TMA bulk store; BatchNorm
+      //      statistics are taken from the staged (stored) values with conflict-free shared-memory reads.
+      const int et = threadIdx.x - 64;          // 0..127 within the epilogue group
+      const int r_in_tile = lane_group * 32 + lane;
+      const int cp = et & 31;                   // column pair handled for statistics
+      const int qtr = et >> 5;                  // 32-row group handled for statistics
+      uint32_t box_counter = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+        const int n0 = nt * p.block_n;
+        mbar_wait(&bars->tmem_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
+        const int nboxes = p.block_n / 64;
+        for (int bx = 0; bx < nboxes; ++bx, ++box_counter) {
+          uint8_t* buf = out_stage + (box_counter & 1) * kStageOutBytes;
+          // the bulk store that read this buffer two boxes ago must have finished reading it
+          if (et == 0 && box_counter >= kOutBufs) tma_store_wait_read<kOutBufs - 1>();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint32_t r[32];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            // statistics are taken of the bf16-rounded value, i.e. of what is stored
-            float v = __bfloat162float(__float2bfloat16(__uint_as_float(r[i])));
-            s1[i] = v;
-            s2[i] = v * v;
-          }
+          for (int half = 0; half < 2; ++half) {
+            tmem_ld_x32(t_row + (uint32_t)(bx * 64 + half * 32), r);
+            tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], 16);
-            s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], 16);
-          }
-#pragma unroll
-          for (int w = 8; w >= 1; w >>= 1) {
-#pragma unroll
-            for (int i = 0; i < w; ++i) {
-              const bool up = (lane & w) != 0;
-              float a1 = up ? s1[i] : s1[i + w], b1 = up ? s1[i + w] : s1[i];
-              float a2 = up ? s2[i] : s2[i + w], b2 = up ? s2[i + w] : s2[i];
-              s1[i] = b1 + __shfl_xor_sync(0xffffffffu, a1, w);
-              s2[i] = b2 + __shfl_xor_sync(0xffffffffu, a2, w);
+            for (int j = 0; j < 4; ++j) {       // four 16-byte chunks of 8 bf16
+              uint4 v;
+              __nv_bfloat162 t;
+#define PK2(a, b) (t = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b)), *reinterpret_cast<uint32_t*>(&t))
+              v.x = PK2(r[8 * j + 0], r[8 * j + 1]);
+              v.y = PK2(r[8 * j + 2], r[8 * j + 3]);
+              v.z = PK2(r[8 * j + 4], r[8 * j + 5]);
+              v.w = PK2(r[8 * j + 6], r[8 * j + 7]);
+#undef PK2
+              const int chunk = half * 4 + j;
+              *reinterpret_cast<uint4*>(buf + r_in_tile * 128 + ((chunk ^ (r_in_tile & 7)) << 4)) = v;
             }
           }
-          // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
-          if (lane < 16) {
-            const int col = lane;
-            float* dst = p.col_stats + ((size_t)mt * 4 + lane_group) * 2 * p.N + n0 + c + col;
-            dst[0] = s1[0];
-            dst[p.N] = s2[0];
+          if (bx == nboxes - 1) {
+            // all of this tile's accumulators are out of TMEM: hand the stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+          }
+          fence_proxy_async();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
+            tma_store_commit();
+          }
+          if (p.col_stats) {
+            float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
+            const int chunk = cp >> 2, word = cp & 3;
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+              const int row = qtr * 32 + i;
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4) + word * 4);
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+              s1a += f.x;
+              s1b += f.y;
+              s2a = fmaf(f.x, f.x, s2a);
+              s2b = fmaf(f.y, f.y, s2b);
+            }
+            float* dst = p.col_stats + ((size_t)mt * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2;
+            *reinterpret_cast<float2*>(dst) = make_float2(s1a, s1b);
+            *reinterpret_cast<float2*>(dst + p.N) = make_float2(s2a, s2b);
           }
         }
-        if (valid && n0 + c < p.N) {
-          if (p.out_fp32) {
-            float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo + n0 + c;
-            if (n0 + c + 16 <= p.N && (p.ldo & 3) == 0) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i)
-                reinterpret_cast<uint4*>(o)[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
-            } else {
-              for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __uint_as_float(r[i]);
+        if (++acc == kAccStages) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+      if (et == 0) tma_store_wait<0>();
+    } else {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+        const int row = mt * kBlockM + lane_group * 32 + lane;
+        const int n0 = nt * p.block_n;
+        mbar_wait(&bars->tmem_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
+        const bool valid = row < p.M;
+        size_t orow = (size_t)row;
+        if (p.scatter && valid) {
+          const int img = row / p.PQ;
+          const int rem = row - img * p.PQ;
+          const int pp = rem / p.Q, qq = rem - pp * p.Q;
+          orow = ((size_t)img * p.H + (size_t)pp * p.sy) * p.W + (size_t)qq * p.sx;
+        }
+        for (int c = 0; c < p.block_n; c += 16) {
+          uint32_t r[16];
+          tmem_ld_x16(t_row + (uint32_t)c, r);
+          tmem_ld_wait();
+          if (p.col_stats) {
+            // per-column sum / sum of squares over this warp's 32 rows (rows past M contribute zeros: their A rows
+            // were zero-filled by TMA), via a halving butterfly: 16+8+4+2+1 shuffles per statistic
+            float s1[16], s2[16];
+  #pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              // statistics are taken of the bf16-rounded value, i.e. of what is stored
+              float v = __bfloat162float(__float2bfloat16(__uint_as_float(r[i])));
+              s1[i] = v;
+              s2[i] = v * v;
             }
-          } else {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + orow * p.ldo + n0 + c;
-            if (n0 + c + 16 <= p.N && (p.ldo & 7) == 0) {
-              store_row_bf16(o, r);
-              if (p.scatter) {
-                // the pixels the strided forward conv never read receive a zero gradient
-                const uint4 z = make_uint4(0, 0, 0, 0);
-                for (int dy = 0; dy < p.sy; ++dy)
-                  for (int dx = 0; dx < p.sx; ++dx) {
-                    if (dy == 0 && dx == 0) continue;
-                    __nv_bfloat16* oz = o + ((size_t)dy * p.W + dx) * p.ldo;
-                    reinterpret_cast<uint4*>(oz)[0] = z;
-                    reinterpret_cast<uint4*>(oz)[1] = z;
-                  }
+  #pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              s1[i] += __shfl_xor_sync(0xffffffffu, s1[i], 16);
+              s2[i] += __shfl_xor_sync(0xffffffffu, s2[i], 16);
+            }
+  #pragma unroll
+            for (int w = 8; w >= 1; w >>= 1) {
+  #pragma unroll
+              for (int i = 0; i < w; ++i) {
+                const bool up = (lane & w) != 0;
+                float a1 = up ? s1[i] : s1[i + w], b1 = up ? s1[i + w] : s1[i];
+                float a2 = up ? s2[i] : s2[i + w], b2 = up ? s2[i + w] : s2[i];
+                s1[i] = b1 + __shfl_xor_sync(0xffffffffu, a1, w);
+                s2[i] = b2 + __shfl_xor_sync(0xffffffffu, a2, w);
+              }
+            }
+            // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
+            if (lane < 16) {
+              const int col = lane;
+              float* dst = p.col_stats + ((size_t)mt * 4 + lane_group) * 2 * p.N + n0 + c + col;
+              dst[0] = s1[0];
+              dst[p.N] = s2[0];
+            }
+          }
+          if (valid && n0 + c < p.N) {
+            if (p.out_fp32) {
+              float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo + n0 + c;
+              if (n0 + c + 16 <= p.N && (p.ldo & 3) == 0) {
+  #pragma unroll
+                for (int i = 0; i < 4; ++i)
+                  reinterpret_cast<uint4*>(o)[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+              } else {
+                for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __uint_as_float(r[i]);
               }
             } else {
-              for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __float2bfloat16(__uint_as_float(r[i]));
+              __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + orow * p.ldo + n0 + c;
+              if (n0 + c + 16 <= p.N && (p.ldo & 7) == 0) {
+                store_row_bf16(o, r);
+                if (p.scatter) {
+                  // the pixels the strided forward conv never read receive a zero gradient
+                  const uint4 z = make_uint4(0, 0, 0, 0);
+                  for (int dy = 0; dy < p.sy; ++dy)
+                    for (int dx = 0; dx < p.sx; ++dx) {
+                      if (dy == 0 && dx == 0) continue;
+                      __nv_bfloat16* oz = o + ((size_t)dy * p.W + dx) * p.ldo;
+                      reinterpret_cast<uint4*>(oz)[0] = z;
+                      reinterpret_cast<uint4*>(oz)[1] = z;
+                    }
+                }
+              } else {
+                for (int i = 0; i < 16 && n0 + c + i < p.N; ++i) o[i] = __float2bfloat16(__uint_as_float(r[i]));
+              }
             }
           }
         }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
-      if (++acc == kAccStages) {
-        acc = 0;
-        acc_phase ^= 1;
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+        if (++acc == kAccStages) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
       }
     }
   }
@@ -314,11 +397,20 @@ int pick_block_n(int n) {
 
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStream_t st) {
   const int stage_bytes = kABytes + p.block_n * kBlockK * 2;
-  int stages = (200 * 1024) / stage_bytes;
+  // bf16 row-major outputs whose tile width is a multiple of 64 go out through shared memory + TMA bulk stores
+  CUtensorMap mo;
+  p.tma_store = (!p.out_fp32 && !p.scatter && p.block_n % 64 == 0 && p.N % 8 == 0 && p.ldo % 8 == 0) ? 1 : 0;
+  if (p.tma_store) {
+    if (tmap_tiled_2d(&mo, p.out, 2, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldo * 2, 64, kBlockM, true)) return -1;
+  } else {
+    mo = ma;   // unused
+  }
+  const int fixed = (int)sizeof(Barriers) + 1024 + (p.tma_store ? kOutBufs * kStageOutBytes : 0);
+  int stages = (227 * 1024 - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   p.stages = stages;
-  const size_t smem = (size_t)stages * stage_bytes + sizeof(Barriers) + 1024;
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -326,7 +418,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-  conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, p);
+  conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, mo, p);
   B200_LAUNCH_CHECK();
   return 0;
 }
