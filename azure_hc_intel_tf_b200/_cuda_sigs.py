@@ -52,7 +52,8 @@ OPTIONAL = {
     "b200_conv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_gemm_nt": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "b200_gemm_nn": (i32, [vp, i32, vp, vp, i32, i32, i32, vp]),
-    "b200_dense_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
+    "b200_dense_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, vp]),
+    "b200_dense_wgrad_workspace_bytes": (i64, [i32, i32, i32]),
     "b200_conv_stats_reduce": (i32, [vp, i64, i32, vp, vp]),
 }
 

@@ -47,8 +47,10 @@ struct WgradParams {
   int kblocks_per_slice;
   int PQ, Q, stride_h, stride_w, base_h, base_w;
   int stages;
-  int atomic;            // 1: red.add into dw, 0: plain stores
+  int atomic;            // 1: red.add into dw, 0: plain stores (to dw, or to this slice's workspace partial)
   float* dw;
+  float* ws;             // when non-null: partial of slice s goes to ws + s * out_elems, a second kernel folds them
+  int64_t out_elems;     // kout * rows_total
 };
 
 struct __align__(8) WBarriers {
@@ -169,6 +171,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     mbar_wait(&bars->tmem_full, 0);
     tc_fence_after();
     const size_t ld = (size_t)p.rows_total;       // dw[k][rows_total]
+    float* const outp = p.ws ? p.ws + (size_t)slice * p.out_elems : p.dw;
     for (int t = 0; t < tiles_here; ++t) {
       const int idx = (tile0 + t) * 128 + lane_group * 32 + lane;
       const bool valid = idx < p.rows_total;
@@ -182,7 +185,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           for (int j = 0; j < 16; ++j) {
             const int ko = n0 + c + j;
             if (ko < p.kout) {
-              float* dst = p.dw + (size_t)ko * ld + idx;
+              float* dst = outp + (size_t)ko * ld + idx;
               if (p.atomic)
                 asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dst), "f"(__uint_as_float(r[j])) : "memory");
               else
@@ -201,6 +204,33 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
+
+// dw[e] = sum over slices of ws[s][e], in slice order (bitwise reproducible).
+__global__ void __launch_bounds__(256) wgrad_fold_kernel(const float* __restrict__ ws, float* __restrict__ dw,
+                                                         int64_t n, int slices) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+    if (i + 4 <= n) {
+      float4 a = __ldcs(reinterpret_cast<const float4*>(ws + i));
+      for (int s2 = 1; s2 < slices; ++s2) {
+        const float4 b = __ldcs(reinterpret_cast<const float4*>(ws + (size_t)s2 * n + i));
+        a.x += b.x;
+        a.y += b.y;
+        a.z += b.z;
+        a.w += b.w;
+      }
+      *reinterpret_cast<float4*>(dw + i) = a;
+    } else {
+      for (int64_t j = i; j < n; ++j) {
+        float a = ws[j];
+        for (int s2 = 1; s2 < slices; ++s2) a += ws[(size_t)s2 * n + j];
+        dw[j] = a;
+      }
+    }
+  }
+}
+
+constexpr int64_t kWorkspaceCap = 96ll << 20;
 
 int plan(const b200_conv_geom* g, WgradParams& p) {
   p.C = g->c;
@@ -221,10 +251,15 @@ int plan(const b200_conv_geom* g, WgradParams& p) {
   p.pix_total = (int64_t)g->n * g->p * g->q;
   p.kblocks_total = (int)((p.pix_total + kBlockK - 1) / kBlockK);
   const int groups = p.m_groups * p.n_tiles;
-  int slices = (2 * kNumSMs + groups - 1) / groups;
+  p.out_elems = (int64_t)g->k * p.rows_total;
+  // one wave of CTAs: as many pixel slices as fit next to the output groups, bounded by the work per slice and by
+  // the size of the partial-sum workspace
+  int slices = kNumSMs / groups;
   int max_slices = p.kblocks_total / 4;
   if (max_slices < 1) max_slices = 1;
   if (slices > max_slices) slices = max_slices;
+  const int64_t by_ws = kWorkspaceCap / (p.out_elems * 4);
+  if (slices > by_ws) slices = (int)by_ws;
   if (slices < 1) slices = 1;
   p.kblocks_per_slice = (p.kblocks_total + slices - 1) / slices;
   p.slices = (p.kblocks_total + p.kblocks_per_slice - 1) / p.kblocks_per_slice;
@@ -256,22 +291,34 @@ int b200_conv_wgrad_supported(const b200_conv_geom* g) {
 }
 
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g) {
-  (void)g;
-  return 0;   // partial sums are combined with red.global.add.f32 directly in dw
+  if (!g || g->c % 64 != 0) return 0;
+  WgradParams p{};
+  plan(g, p);
+  return p.slices > 1 ? (int64_t)p.slices * p.out_elems * 4 : 0;
 }
 
 static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
-                      void* stream);
+                      void* workspace, void* stream);
 
 int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
                     void* stream) {
-  (void)workspace;
   B200_CHECK_ARG(g, "conv_wgrad: null geometry");
-  return wgrad_impl(x, dy, dw, g, g->k, stream);
+  return wgrad_impl(x, dy, dw, g, g->k, workspace, stream);
+}
+
+int64_t b200_dense_wgrad_workspace_bytes(int32_t batch, int32_t in_features, int32_t out_features) {
+  b200_conv_geom g{};
+  g.n = batch;
+  g.h = g.w = g.p = g.q = 1;
+  g.c = in_features;
+  g.k = out_features;
+  g.r = g.s = 1;
+  g.stride_h = g.stride_w = 1;
+  return b200_conv_wgrad_workspace_bytes(&g);
 }
 
 int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t batch, int32_t in_features,
-                     int32_t out_features, int32_t dy_ld, void* stream) {
+                     int32_t out_features, int32_t dy_ld, void* workspace, void* stream) {
   B200_CHECK_ARG(dy_ld >= out_features && dy_ld % 8 == 0, "dense_wgrad: dy_ld must be >= out and a multiple of 8");
   b200_conv_geom g{};
   g.n = batch;
@@ -280,11 +327,11 @@ int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t
   g.k = out_features;
   g.r = g.s = 1;
   g.stride_h = g.stride_w = 1;
-  return wgrad_impl(x, dy, dw, &g, dy_ld, stream);
+  return wgrad_impl(x, dy, dw, &g, dy_ld, workspace, stream);
 }
 
 static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
-                      void* stream) {
+                      void* workspace, void* stream) {
   B200_CHECK_ARG(x && dy && dw && g, "conv_wgrad: null pointer");
   B200_CHECK_ARG(g->c % 64 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
                  "conv_wgrad: unsupported geometry (need Cin%%64==0, dy row stride %%8==0)");
@@ -298,7 +345,14 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
                        64, kBlockK))
     return -1;
   if (tmap_tiled_2d(&mdy, dy, 2, (uint64_t)dy_ld, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, 64, kBlockK, true)) return -1;
-  if (p.atomic) B200_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)g->k * p.rows_total, st));
+  // several pixel slices: partials go to the workspace and are folded in a fixed order; without a workspace they
+  // are combined with float atomics directly in dw (not bitwise reproducible)
+  if (p.slices > 1 && workspace) {
+    p.ws = static_cast<float*>(workspace);
+    p.atomic = 0;
+  } else if (p.atomic) {
+    B200_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)p.out_elems, st));
+  }
   const int nb = (p.block_n + 63) / 64;
   const size_t smem = (size_t)p.stages * (p.T * 2 * kBox + nb * kBox) + sizeof(WBarriers) + 1024;
   static bool attr_set = false;
@@ -309,6 +363,11 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
   const int grid = p.slices * p.m_groups * p.n_tiles;
   conv_wgrad_kernel<<<grid, kThreads, smem, st>>>(mx, mdy, p);
   B200_LAUNCH_CHECK();
+  if (p.ws) {
+    const int64_t vec = (p.out_elems + 3) / 4;
+    wgrad_fold_kernel<<<grid_for(vec, 256, 4), 256, 0, st>>>(p.ws, dw, p.out_elems, p.slices);
+    B200_LAUNCH_CHECK();
+  }
   return 0;
 }
 

@@ -77,19 +77,25 @@ def dgrad(dy, w_lp, m, x_shape):
 _ws = {}
 
 
+def _workspace(need, device):
+    """Split-K partial-sum workspace, one per device and stream (kernels using it are ordered on that stream)."""
+    if need <= 0:
+        return None
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 100 << 20), dtype=torch.uint8, device=device)
+        _ws[key] = ws
+    return ws
+
+
 def wgrad(x, dy, m, out=None):
     g = geom(x.shape, m)
     if out is None:
         out = torch.empty((g.k, g.r, g.s, g.c), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
-    need = lib().b200_conv_wgrad_workspace_bytes(C.byref(g))
-    ws = None
-    if need > 0:
-        key = x.device.index
-        ws = _ws.get(key)
-        if ws is None or ws.numel() < need:
-            ws = torch.empty(max(need, 64 << 20), dtype=torch.uint8, device=x.device)
-            _ws[key] = ws
+    ws = _workspace(lib().b200_conv_wgrad_workspace_bytes(C.byref(g)), x.device)
     _check(lib().b200_conv_wgrad(_ptr(x), _ptr(dy), _ptr(out), C.byref(g), _ptr(ws), _stream()), "conv_wgrad")
+    b200.count_launch(1 if ws is not None else 0)
     return out
 
 
@@ -116,5 +122,8 @@ def dense_wgrad(x, dy, out_features, out=None):
     ld = dy.shape[1]
     if out is None:
         out = torch.empty((out_features, infe), dtype=torch.float32, device=x.device)
-    _check(lib().b200_dense_wgrad(_ptr(x), _ptr(dy), _ptr(out), bsz, infe, out_features, ld, _stream()), "dense_wgrad")
+    ws = _workspace(lib().b200_dense_wgrad_workspace_bytes(bsz, infe, out_features), x.device)
+    _check(lib().b200_dense_wgrad(_ptr(x), _ptr(dy), _ptr(out), bsz, infe, out_features, ld, _ptr(ws), _stream()),
+           "dense_wgrad")
+    b200.count_launch(1 if ws is not None else 0)
     return out

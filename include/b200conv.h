@@ -41,8 +41,9 @@ int64_t b200_conv_stats_rows(const b200_conv_geom* g);
 /* dx = gradient of fprop wrt x. Stride 1 (any filter), or strided 1x1 without padding. */
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);
 
-/* dw[k,r,s,c] (fp32) = sum over pixels of dy[.,k] * x[window]. dw is overwritten. `workspace` must hold
- * b200_conv_wgrad_workspace_bytes(g) bytes (may be NULL when that is 0). */
+/* dw[k,r,s,c] (fp32) = sum over pixels of dy[.,k] * x[window]. dw is overwritten. The pixel range is split over
+ * CTAs; with `workspace` of b200_conv_wgrad_workspace_bytes(g) bytes the per-slice partials are folded in a fixed
+ * order (bitwise reproducible); with workspace == NULL they are combined with float atomics in dw instead. */
 int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
                     void* stream);
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
@@ -59,7 +60,8 @@ int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16*
 /* Dense-layer weight gradient: dw[out][in] (fp32, overwritten) = dy[batch][out]^T . x[batch][in]; dy rows have
  * leading dimension dy_ld (multiple of 8, >= out; the padding columns are ignored). in % 64 == 0. */
 int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t batch, int32_t in_features,
-                     int32_t out_features, int32_t dy_ld, void* stream);
+                     int32_t out_features, int32_t dy_ld, void* workspace, void* stream);
+int64_t b200_dense_wgrad_workspace_bytes(int32_t batch, int32_t in_features, int32_t out_features);
 
 /* Reduce the per-group partials written by b200_conv_fprop into sums[0..k) = Σy, sums[k..2k) = Σy². */
 int b200_conv_stats_reduce(const float* col_stats, int64_t rows, int32_t k, float* sums, void* stream);
