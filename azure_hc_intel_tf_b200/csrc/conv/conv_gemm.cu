@@ -50,7 +50,7 @@ struct GemmParams {
   int out_fp32;
   // strided 1x1 dgrad: GEMM row (n,p,q) lands at (n, p*sy, q*sx) of an H x W image; the other pixels get zeros
   int scatter, sy, sx, H, W;
-  float* col_stats;       // optional [num_m_tiles*4][2][N] per-32-row-group column sums / sums of squares (BN statistics)
+  float* col_stats;       // optional [gridDim.x*4][2][N]: per (CTA, 32-row group) running column sums / sums of squares
   int tma_store;          // epilogue stages bf16 tiles in shared memory and writes them with TMA bulk stores
 };
 
@@ -221,6 +221,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int nboxes = p.block_n / 64;
         for (int bx = 0; bx < nboxes; ++bx, ++box_counter) {
           uint8_t* buf = out_stage + (box_counter & 1) * kStageOutBytes;
+          // this CTA's running column statistics for (row group qtr, column pair cp) of this box: fetched now, the
+          // latency hides behind the TMEM loads below; only this thread ever touches these addresses
+          float* const st_dst = p.col_stats
+                                    ? p.col_stats + ((size_t)blockIdx.x * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
+                                    : nullptr;
+          float2 old1 = make_float2(0.f, 0.f), old2 = make_float2(0.f, 0.f);
+          if (st_dst) {
+            old1 = __ldcg(reinterpret_cast<const float2*>(st_dst));
+            old2 = __ldcg(reinterpret_cast<const float2*>(st_dst + p.N));
+          }
           // the bulk store that read this buffer two boxes ago must have finished reading it
           if (et == 0 && box_counter >= kOutBufs) tma_store_wait_read<kOutBufs - 1>();
           asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -268,9 +278,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               s2a = fmaf(f.x, f.x, s2a);
               s2b = fmaf(f.y, f.y, s2b);
             }
-            float* dst = p.col_stats + ((size_t)mt * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2;
-            *reinterpret_cast<float2*>(dst) = make_float2(s1a, s1b);
-            *reinterpret_cast<float2*>(dst + p.N) = make_float2(s2a, s2b);
+            __stcg(reinterpret_cast<float2*>(st_dst), make_float2(old1.x + s1a, old1.y + s1b));
+            __stcg(reinterpret_cast<float2*>(st_dst + p.N), make_float2(old2.x + s2a, old2.y + s2b));
           }
         }
         if (++acc == kAccStages) {
@@ -329,9 +338,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
             if (lane < 16) {
               const int col = lane;
-              float* dst = p.col_stats + ((size_t)mt * 4 + lane_group) * 2 * p.N + n0 + c + col;
-              dst[0] = s1[0];
-              dst[p.N] = s2[0];
+              float* dst = p.col_stats + ((size_t)blockIdx.x * 4 + lane_group) * 2 * p.N + n0 + c + col;
+              dst[0] += s1[0];
+              dst[p.N] += s2[0];
             }
           }
           if (valid && n0 + c < p.N) {
@@ -480,13 +489,19 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   p.out = y;
   p.ldo = g->k;
   p.col_stats = col_stats;
+  if (col_stats)   // per-CTA running sums start at zero
+    B200_CUDA(cudaMemsetAsync(col_stats, 0, sizeof(float) * 2 * (size_t)g->k * (size_t)b200_conv_stats_rows(g),
+                              static_cast<cudaStream_t>(stream)));
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 
 int64_t b200_conv_stats_rows(const b200_conv_geom* g) {
+  // one row per (CTA, 32-row group): the persistent grid has at most one CTA per SM
   if (!g) return -1;
   const int64_t m = (int64_t)g->n * g->p * g->q;
-  return (m + kBlockM - 1) / kBlockM * 4;
+  const int bn = pick_block_n(g->k);
+  int64_t tiles = (m + kBlockM - 1) / kBlockM * ((g->k + bn - 1) / bn);
+  return (tiles < kNumSMs ? tiles : kNumSMs) * 4;
 }
 
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream) {

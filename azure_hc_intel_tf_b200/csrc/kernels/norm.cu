@@ -3,23 +3,24 @@
 // Role in the reference stack: MKL-DNN's fused batch-normalisation and eltwise primitives that TensorFlow
 // calls under --mkl=TRUE (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:76); K4/K5/K6 in SURVEY.md §2.6.
 //
-// All reductions over rows share one column-reduce skeleton: a block owns TY rows x all channels per
-// iteration (each thread 8 channels = one 16-byte load), accumulates in fp32 registers, folds TY in shared
-// memory, writes one partial per block into caller-provided scratch, and the last block to finish (ticket
-// counter in scratch[0]) folds the partials in a fixed order and runs the policy's finalisation. Results are
-// therefore bitwise reproducible run to run.
+// Column reductions (statistics, dgamma/dbeta, dbias) share one skeleton: a block covers 64 channels (8 threads x
+// one 16-byte vector) x 32 rows per trip, four rows in flight per thread, per-channel constants held in registers;
+// partial sums go to caller-provided scratch and the last block of each channel chunk (ticket counter in the
+// scratch header) folds them in a fixed order, so results are bitwise reproducible run to run.
+// Elementwise passes keep each thread on a fixed channel vector (grid stride is a multiple of C/8 whenever C/8
+// divides 256), so scale/shift and the backward coefficients are loaded once per thread, not once per element.
 #include "common.cuh"
 
 namespace b200 {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxBlocks = 2 * kNumSMs;
-constexpr int kScratchHeader = 64;  // floats reserved in front of the partials (ticket lives at [0])
+constexpr int kTargetBlocks = 8 * kNumSMs;   // enough CTAs for ~8 per SM: the passes are latency/bandwidth bound
+constexpr int kScratchHeader = 64;           // floats reserved in front of the partials (one ticket per channel chunk)
 
 struct ColGeom {
-  int tx;       // threads across channels (each 8 channels)
-  int ty;       // rows per block iteration
+  int tx;       // threads across channels (each 8 channels); 8 = 64 channels per block
+  int ty;       // rows per block trip
   int cvecs;    // c / 8
   int ychunks;  // grid.y: channel chunks of tx vectors
   int blocks;   // grid.x
@@ -28,17 +29,17 @@ struct ColGeom {
 inline ColGeom col_geom(int64_t rows, int c) {
   ColGeom g;
   g.cvecs = c / 8;
-  g.tx = g.cvecs < kThreads ? g.cvecs : kThreads;
+  g.tx = g.cvecs < 8 ? g.cvecs : 8;
   g.ty = kThreads / g.tx;
   g.ychunks = (g.cvecs + g.tx - 1) / g.tx;
-  int64_t b = (rows + (int64_t)g.ty * 8 - 1) / ((int64_t)g.ty * 8);
-  int cap = kMaxBlocks / g.ychunks;
+  int64_t b = (rows + (int64_t)g.ty * 4 - 1) / ((int64_t)g.ty * 4);
+  int cap = kTargetBlocks / g.ychunks;
   if (cap < 1) cap = 1;
   g.blocks = (int)(b < 1 ? 1 : (b > cap ? cap : b));
   return g;
 }
 
-// ---- policies -------------------------------------------------------------------------------------
+// ---- policies: prepare(cv) caches per-channel constants, load() accumulates one row ---------------------
 
 struct StatsPolicy {
   const b200_bf16* x;
@@ -49,18 +50,17 @@ struct StatsPolicy {
   int64_t rows;
   int c;
 
+  __device__ __forceinline__ void prepare(int) {}
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float f[8];
     unpack8(ld8_stream(x + row * c + cv * 8), f);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       a[i] += f[i];
-      b[i] += f[i] * f[i];
+      b[i] = fmaf(f[i], f[i], b[i]);
     }
   }
-  __device__ __forceinline__ void finalize(int ch, float s1, float s2) const {
-    bn_finish(ch, s1, s2);
-  }
+  __device__ __forceinline__ void finalize(int ch, float s1, float s2) const { bn_finish(ch, s1, s2); }
   __device__ __forceinline__ void bn_finish(int ch, float s1, float s2) const {
     float inv = 1.0f / (float)rows;
     float m = s1 * inv;
@@ -86,27 +86,38 @@ struct BwdReducePolicy {
   int relu;
   float *dgamma, *dbeta;
   int c;
+  float k_mean[8], k_rstd[8], k_scale[8], k_shift[8];
 
+  __device__ __forceinline__ void prepare(int cv) {
+    const int ch = cv * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      k_mean[i] = mean[ch + i];
+      k_rstd[i] = rstd[ch + i];
+      k_scale[i] = scale[ch + i];
+      k_shift[i] = shift[ch + i];
+    }
+  }
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float g[8], xv[8];
-    int ch = cv * 8;
-    unpack8(ld8_stream(dz + row * c + ch), g);
-    unpack8(ld8_stream(x + row * c + ch), xv);
+    const int64_t off = row * c + cv * 8;
+    unpack8(ld8_stream(dz + off), g);
+    unpack8(ld8_stream(x + off), xv);
     if (relu) {
       if (z) {
         float zv[8];
-        unpack8(ld8_stream(z + row * c + ch), zv);
+        unpack8(ld8_stream(z + off), zv);
 #pragma unroll
         for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
       } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) g[i] = (scale[ch + i] * xv[i] + shift[ch + i]) > 0.0f ? g[i] : 0.0f;
+        for (int i = 0; i < 8; ++i) g[i] = fmaf(k_scale[i], xv[i], k_shift[i]) > 0.0f ? g[i] : 0.0f;
       }
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      a[i] += g[i];                                              // dbeta
-      b[i] += g[i] * (xv[i] - mean[ch + i]) * rstd[ch + i];      // dgamma
+      a[i] += g[i];                                                    // dbeta
+      b[i] = fmaf(g[i], (xv[i] - k_mean[i]) * k_rstd[i], b[i]);        // dgamma
     }
   }
   __device__ __forceinline__ void finalize(int ch, float s1, float s2) const {
@@ -122,21 +133,23 @@ struct BiasBwdPolicy {
   int relu;
   int c;
 
+  __device__ __forceinline__ void prepare(int) {}
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float g[8];
-    int ch = cv * 8;
-    unpack8(ld8_stream(dz + row * c + ch), g);
+    const int64_t off = row * c + cv * 8;
+    unpack8(ld8_stream(dz + off), g);
     if (relu) {
       float zv[8];
-      unpack8(ld8_stream(z + row * c + ch), zv);
+      unpack8(ld8_stream(z + off), zv);
 #pragma unroll
       for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
-      if (dx) st8(dx + row * c + ch, pack8(g));
+      if (dx) st8(dx + off, pack8(g));
     } else if (dx && dx != dz) {
-      st8(dx + row * c + ch, pack8(g));
+      st8(dx + off, pack8(g));
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) a[i] += g[i];
+    (void)b;
   }
   __device__ __forceinline__ void finalize(int ch, float s1, float) const { dbias[ch] = s1; }
 };
@@ -144,8 +157,8 @@ struct BiasBwdPolicy {
 // ---- skeleton -------------------------------------------------------------------------------------
 
 template <class Policy>
-__global__ void __launch_bounds__(kThreads) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
-                                                              float* scratch) {
+__global__ void __launch_bounds__(kThreads, 2) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
+                                                                 float* scratch) {
   __shared__ float sm[kThreads * 16];
   __shared__ int is_last;
   const int tid = threadIdx.x;
@@ -156,14 +169,17 @@ __global__ void __launch_bounds__(kThreads) col_reduce_kernel(Policy pol, int64_
 #pragma unroll
   for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.0f;
   if (active) {
+    pol.prepare(cv);
     const int64_t stride = (int64_t)gridDim.x * g.ty;
     int64_t r = (int64_t)blockIdx.x * g.ty + ty;
-    // two rows per trip keeps two independent 16-byte loads per operand in flight
-    for (; r + stride < rows; r += 2 * stride) {
+    // four rows per trip: four independent groups of 16-byte loads in flight per thread
+    for (; r + 3 * stride < rows; r += 4 * stride) {
       pol.load(r, cv, a, b);
       pol.load(r + stride, cv, a, b);
+      pol.load(r + 2 * stride, cv, a, b);
+      pol.load(r + 3 * stride, cv, a, b);
     }
-    if (r < rows) pol.load(r, cv, a, b);
+    for (; r < rows; r += stride) pol.load(r, cv, a, b);
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -171,14 +187,14 @@ __global__ void __launch_bounds__(kThreads) col_reduce_kernel(Policy pol, int64_
     sm[(8 + i) * kThreads + tid] = b[i];
   }
   __syncthreads();
-  float* partial = scratch + kScratchHeader + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * (size_t)(g.tx * 16);
-  if (ty == 0 && cv < g.cvecs) {
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      float s = 0.0f;
-      for (int y = 0; y < g.ty; ++y) s += sm[i * kThreads + y * g.tx + tx];
-      partial[i * g.tx + tx] = s;
-    }
+  // fold the ty row-lanes: thread j < 16*tx sums column (j % tx) of quantity (j / tx)
+  const int per_block = g.tx * 16;
+  float* partial = scratch + kScratchHeader + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * (size_t)per_block;
+  if (tid < per_block) {
+    const int i = tid / g.tx, x = tid % g.tx;
+    float s = 0.0f;
+    for (int y = 0; y < g.ty; ++y) s += sm[i * kThreads + y * g.tx + x];
+    partial[i * g.tx + x] = s;
   }
   __threadfence();
   __syncthreads();
@@ -190,19 +206,42 @@ __global__ void __launch_bounds__(kThreads) col_reduce_kernel(Policy pol, int64_
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  // last block of this channel chunk: fold the per-block partials in block order
-  const float* base = scratch + kScratchHeader + (size_t)blockIdx.y * gridDim.x * (size_t)(g.tx * 16);
-  for (int j = tid; j < g.tx * 8; j += kThreads) {
-    int i = j / g.tx, x = j % g.tx;   // element i of vector x
-    int cvv = blockIdx.y * g.tx + x;
-    if (cvv >= g.cvecs) continue;
-    float s1 = 0.0f, s2 = 0.0f;
-    for (unsigned int bk = 0; bk < gridDim.x; ++bk) {
-      const float* p = base + (size_t)bk * (g.tx * 16);
-      s1 += __ldcg(p + i * g.tx + x);
-      s2 += __ldcg(p + (8 + i) * g.tx + x);
+  // last block of this channel chunk: fold the per-block partials. per_block (<= 128) outputs, 256 threads:
+  // `seg` threads share one output, each summing a contiguous range of blocks; ranges are combined in order.
+  const float* base = scratch + kScratchHeader + (size_t)blockIdx.y * gridDim.x * (size_t)per_block;
+  const int seg = kThreads / per_block;              // >= 2
+  const int j = tid % per_block, sg = tid / per_block;
+  float acc = 0.0f;
+  if (sg < seg) {
+    const int nb = (int)gridDim.x;
+    const int lo = (int)((int64_t)nb * sg / seg), hi = (int)((int64_t)nb * (sg + 1) / seg);
+    int bk = lo;
+    for (; bk + 4 <= hi; bk += 4) {
+      const float v0 = __ldcg(base + (size_t)bk * per_block + j);
+      const float v1 = __ldcg(base + (size_t)(bk + 1) * per_block + j);
+      const float v2 = __ldcg(base + (size_t)(bk + 2) * per_block + j);
+      const float v3 = __ldcg(base + (size_t)(bk + 3) * per_block + j);
+      acc += v0;
+      acc += v1;
+      acc += v2;
+      acc += v3;
     }
-    pol.finalize(cvv * 8 + i, s1, s2);
+    for (; bk < hi; ++bk) acc += __ldcg(base + (size_t)bk * per_block + j);
+  }
+  __syncthreads();
+  sm[tid] = acc;
+  __syncthreads();
+  if (tid < g.tx * 8) {
+    const int i = tid / g.tx, x = tid % g.tx;      // quantity-1 element i of vector x; quantity 2 is at i + 8
+    const int cvv = blockIdx.y * g.tx + x;
+    if (cvv < g.cvecs) {
+      float s1 = 0.0f, s2 = 0.0f;
+      for (int q = 0; q < seg; ++q) {
+        s1 += sm[q * per_block + i * g.tx + x];
+        s2 += sm[q * per_block + (8 + i) * g.tx + x];
+      }
+      pol.finalize(cvv * 8 + i, s1, s2);
+    }
   }
   if (tid == 0) *ticket = 0u;   // leave the counter armed for the next call
 }
@@ -210,6 +249,7 @@ __global__ void __launch_bounds__(kThreads) col_reduce_kernel(Policy pol, int64_
 template <class Policy>
 int launch_col_reduce(const Policy& pol, int64_t rows, int c, void* scratch, cudaStream_t st) {
   ColGeom g = col_geom(rows, c);
+  B200_CHECK_ARG(g.ychunks <= kScratchHeader, "column reduce: too many channels (c=%d)", c);
   dim3 grid(g.blocks, g.ychunks);
   col_reduce_kernel<Policy><<<grid, kThreads, 0, st>>>(pol, rows, c, g, static_cast<float*>(scratch));
   B200_LAUNCH_CHECK();
@@ -217,70 +257,147 @@ int launch_col_reduce(const Policy& pol, int64_t rows, int c, void* scratch, cud
 }
 
 // ---- elementwise ----------------------------------------------------------------------------------
+// Vector index v = row * cvecs + cv. When `fixed` (grid stride % cvecs == 0) a thread's cv never changes.
+
+struct ElemGrid {
+  int blocks;
+  int fixed;
+};
+
+inline ElemGrid elem_grid(int64_t nvec, int cvecs) {
+  ElemGrid e;
+  int64_t b = (nvec + 256 * 4 - 1) / (256 * 4);
+  if (b > kTargetBlocks) b = kTargetBlocks;
+  if (b < 1) b = 1;
+  e.fixed = (256 % cvecs == 0) ? 1 : 0;
+  if (!e.fixed) {
+    // make the stride a multiple of cvecs anyway when a nearby block count allows it
+    for (int64_t t = b; t > 0 && t > b - cvecs; --t)
+      if ((t * 256) % cvecs == 0) {
+        b = t;
+        e.fixed = 1;
+        break;
+      }
+  }
+  e.blocks = (int)b;
+  return e;
+}
+
+__device__ __forceinline__ void load8f(const float* p, float o[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
 
 __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restrict__ x, const b200_bf16* __restrict__ res,
                                                        b200_bf16* __restrict__ z, int64_t nvec, int cvecs,
                                                        const float* __restrict__ scale, const float* __restrict__ shift,
-                                                       int relu) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                       int relu, int fixed) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < nvec; i += stride) {
-    int ch = (int)(i % cvecs) * 8;
-    float f[8];
-    unpack8(ld8_stream(x + i * 8), f);
-    float4 s0 = *reinterpret_cast<const float4*>(scale + ch), s1 = *reinterpret_cast<const float4*>(scale + ch + 4);
-    float4 h0 = *reinterpret_cast<const float4*>(shift + ch), h1 = *reinterpret_cast<const float4*>(shift + ch + 4);
-    float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-#pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sh[k]);
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float sc[8], sh[8];
+  if (fixed && i < nvec) {
+    const int ch = (int)(i % cvecs) * 8;
+    load8f(scale + ch, sc);
+    load8f(shift + ch, sh);
+  }
+  for (; i < nvec; i += 2 * stride) {
+    const bool two = i + stride < nvec;
+    bf16x8 v0 = ld8_stream(x + i * 8), v1, r0, r1;
+    if (two) v1 = ld8_stream(x + (i + stride) * 8);
     if (res) {
-      float r[8];
-      unpack8(ld8_stream(res + i * 8), r);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] += r[k];
+      r0 = ld8_stream(res + i * 8);
+      if (two) r1 = ld8_stream(res + (i + stride) * 8);
     }
-    if (relu) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.0f);
+    for (int k2 = 0; k2 < 2; ++k2) {
+      if (k2 == 1 && !two) break;
+      const int64_t idx = k2 ? i + stride : i;
+      if (!fixed) {
+        const int ch = (int)(idx % cvecs) * 8;
+        load8f(scale + ch, sc);
+        load8f(shift + ch, sh);
+      }
+      float f[8];
+      unpack8(k2 ? v1 : v0, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sh[k]);
+      if (res) {
+        float r[8];
+        unpack8(k2 ? r1 : r0, r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] += r[k];
+      }
+      if (relu) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.0f);
+      }
+      st8(z + idx * 8, pack8(f));
     }
-    st8(z + i * 8, pack8(f));
   }
 }
 
+// dx = A*g + B*x + C with g = dz masked by the ReLU; A = scale, B = -scale*dgamma*rstd/M, C = -scale*dbeta/M - B*mean
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const b200_bf16* __restrict__ dz, const b200_bf16* __restrict__ x,
                                                            const b200_bf16* __restrict__ z, b200_bf16* __restrict__ dx,
                                                            b200_bf16* __restrict__ dres, int64_t nvec, int cvecs,
                                                            float inv_rows, const float* __restrict__ mean,
                                                            const float* __restrict__ rstd, const float* __restrict__ scale,
                                                            const float* __restrict__ shift, const float* __restrict__ dgamma,
-                                                           const float* __restrict__ dbeta, int relu) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                           const float* __restrict__ dbeta, int relu, int fixed) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < nvec; i += stride) {
-    int ch = (int)(i % cvecs) * 8;
-    float g[8], xv[8];
-    unpack8(ld8_stream(dz + i * 8), g);
-    unpack8(ld8_stream(x + i * 8), xv);
-    if (relu) {
-      if (z) {
-        float zv[8];
-        unpack8(ld8_stream(z + i * 8), zv);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] = zv[k] > 0.0f ? g[k] : 0.0f;
-      } else {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] = fmaf(scale[ch + k], xv[k], shift[ch + k]) > 0.0f ? g[k] : 0.0f;
-      }
-    }
-    if (dres) st8(dres + i * 8, pack8(g));
-    float o[8];
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float cA[8], cB[8], cC[8], cS[8];
+  auto coeffs = [&](int ch) {
+    float m[8], r[8], dg[8], db[8];
+    load8f(scale + ch, cA);
+    load8f(shift + ch, cS);
+    load8f(mean + ch, m);
+    load8f(rstd + ch, r);
+    load8f(dgamma + ch, dg);
+    load8f(dbeta + ch, db);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      float xhat = (xv[k] - mean[ch + k]) * rstd[ch + k];
-      o[k] = scale[ch + k] * (g[k] - dbeta[ch + k] * inv_rows - xhat * dgamma[ch + k] * inv_rows);
+      cB[k] = -cA[k] * dg[k] * r[k] * inv_rows;
+      cC[k] = -cA[k] * db[k] * inv_rows - cB[k] * m[k];
     }
-    st8(dx + i * 8, pack8(o));
+  };
+  if (fixed && i < nvec) coeffs((int)(i % cvecs) * 8);
+  for (; i < nvec; i += 2 * stride) {
+    const bool two = i + stride < nvec;
+    bf16x8 g0 = ld8_stream(dz + i * 8), x0 = ld8_stream(x + i * 8), g1, x1, z0, z1;
+    if (two) {
+      g1 = ld8_stream(dz + (i + stride) * 8);
+      x1 = ld8_stream(x + (i + stride) * 8);
+    }
+    if (relu && z) {
+      z0 = ld8_stream(z + i * 8);
+      if (two) z1 = ld8_stream(z + (i + stride) * 8);
+    }
+#pragma unroll
+    for (int k2 = 0; k2 < 2; ++k2) {
+      if (k2 == 1 && !two) break;
+      const int64_t idx = k2 ? i + stride : i;
+      if (!fixed) coeffs((int)(idx % cvecs) * 8);
+      float g[8], xv[8];
+      unpack8(k2 ? g1 : g0, g);
+      unpack8(k2 ? x1 : x0, xv);
+      if (relu) {
+        if (z) {
+          float zv[8];
+          unpack8(k2 ? z1 : z0, zv);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) g[k] = zv[k] > 0.0f ? g[k] : 0.0f;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) g[k] = fmaf(cA[k], xv[k], cS[k]) > 0.0f ? g[k] : 0.0f;
+        }
+      }
+      if (dres) st8(dres + idx * 8, pack8(g));
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = fmaf(cA[k], g[k], fmaf(cB[k], xv[k], cC[k]));
+      st8(dx + idx * 8, pack8(o));
+    }
   }
 }
 
@@ -304,6 +421,36 @@ __global__ void __launch_bounds__(256) bias_act_kernel(const b200_bf16* __restri
 __global__ void bn_finalize_kernel(StatsPolicy pol, const float* sums, int c) {
   int ch = blockIdx.x * blockDim.x + threadIdx.x;
   if (ch < c) pol.bn_finish(ch, sums[ch], sums[c + ch]);
+}
+
+// Fold [nrows][2][c] partial sums (conv epilogue) in row order, then finalise. Block = 32 channels x 8 row slices.
+__global__ void __launch_bounds__(256) bn_finalize_partials_kernel(StatsPolicy pol, const float* __restrict__ part,
+                                                                   int64_t nrows, int c) {
+  __shared__ float sm[2][8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int ch = blockIdx.x * 32 + tx;
+  float s1 = 0.0f, s2 = 0.0f;
+  if (ch < c) {
+    // contiguous row ranges per slice keep the summation order fixed
+    const int64_t lo = nrows * ty / 8, hi = nrows * (ty + 1) / 8;
+    for (int64_t r = lo; r < hi; ++r) {
+      const float* p = part + r * 2 * c;
+      s1 += __ldcg(p + ch);
+      s2 += __ldcg(p + c + ch);
+    }
+  }
+  sm[0][ty][tx] = s1;
+  sm[1][ty][tx] = s2;
+  __syncthreads();
+  if (ty == 0 && ch < c) {
+    float a = 0.0f, b = 0.0f;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) {
+      a += sm[0][y][tx];
+      b += sm[1][y][tx];
+    }
+    pol.bn_finish(ch, a, b);
+  }
 }
 
 __global__ void __launch_bounds__(256) add_kernel(const b200_bf16* __restrict__ a, const b200_bf16* __restrict__ b,
@@ -366,13 +513,24 @@ int b200_bn_finalize(const float* sums, int64_t rows, int32_t c, const float* ga
   return 0;
 }
 
+int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows, int32_t c, const float* gamma,
+                              const float* beta, float* running_mean, float* running_var, float decay, float eps,
+                              float* mean, float* rstd, float* scale, float* shift, void* stream) {
+  B200_CHECK_ARG(partials && mean && rstd && scale && shift && nrows > 0, "bn_finalize_partials: bad args");
+  StatsPolicy pol{nullptr, gamma, beta, running_mean, running_var, decay, eps, mean, rstd, scale, shift, rows, c};
+  bn_finalize_partials_kernel<<<(c + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(pol, partials, nrows, c);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
 int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, int64_t rows, int32_t c,
                   const float* scale, const float* shift, int32_t relu, void* stream) {
   B200_CHECK_ARG(x && z && scale && shift, "bn_apply: null pointer");
   B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_apply: need c%%8==0 (c=%d)", c);
   int64_t nvec = rows * (c / 8);
-  bn_apply_kernel<<<grid_for(nvec, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, residual, z, nvec, c / 8,
-                                                                                     scale, shift, relu);
+  ElemGrid e = elem_grid(nvec, c / 8);
+  bn_apply_kernel<<<e.blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, residual, z, nvec, c / 8, scale, shift,
+                                                                          relu, e.fixed);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -392,8 +550,9 @@ int b200_bn_bwd_apply(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* 
   B200_CHECK_ARG(dz && x && dx && mean && rstd && scale && shift && dgamma && dbeta, "bn_bwd_apply: null pointer");
   B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_bwd_apply: need c%%8==0 (c=%d)", c);
   int64_t nvec = rows * (c / 8);
-  bn_bwd_apply_kernel<<<grid_for(nvec, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      dz, x, z, dx, dres, nvec, c / 8, 1.0f / (float)rows, mean, rstd, scale, shift, dgamma, dbeta, relu);
+  ElemGrid e = elem_grid(nvec, c / 8);
+  bn_bwd_apply_kernel<<<e.blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      dz, x, z, dx, dres, nvec, c / 8, 1.0f / (float)rows, mean, rstd, scale, shift, dgamma, dbeta, relu, e.fixed);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -97,8 +97,8 @@ def lowp(p: torch.Tensor) -> torch.Tensor:
 # ------------------------------------------------------------------------------------ BN pieces
 
 def bn_forward(y, bn, residual, relu, sums=None):
-    """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift). ``sums`` ([2,C]
-    fp32 Σy, Σy²) comes from the conv epilogue when available, which saves one read of y."""
+    """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift). ``sums``
+    ([rows,2,C] fp32 partial Σy, Σy²) comes from the conv epilogue when available, which saves one read of y."""
     n, c, h, w = y.shape
     rows = n * h * w
     dev = y.device
@@ -106,9 +106,10 @@ def bn_forward(y, bn, residual, relu, sums=None):
     mean, rstd, scale, shift = stats[0], stats[1], stats[2], stats[3]
     training = bn.training
     if training and sums is not None:
-        _check(lib().b200_bn_finalize(_ptr(sums), rows, c, _ptr(bn.gamma), _ptr(bn.beta), _ptr(bn.moving_mean),
-                                      _ptr(bn.moving_variance), bn.decay, bn.eps, _ptr(mean), _ptr(rstd), _ptr(scale),
-                                      _ptr(shift), _stream()), "bn_finalize")
+        _check(lib().b200_bn_finalize_partials(_ptr(sums), sums.shape[0], rows, c, _ptr(bn.gamma), _ptr(bn.beta),
+                                               _ptr(bn.moving_mean), _ptr(bn.moving_variance), bn.decay, bn.eps,
+                                               _ptr(mean), _ptr(rstd), _ptr(scale), _ptr(shift), _stream()),
+               "bn_finalize_partials")
     elif training:
         _check(lib().b200_bn_stats(_ptr(y), rows, c, _ptr(bn.gamma), _ptr(bn.beta), _ptr(bn.moving_mean),
                                    _ptr(bn.moving_variance), bn.decay, bn.eps, _ptr(mean), _ptr(rstd), _ptr(scale),

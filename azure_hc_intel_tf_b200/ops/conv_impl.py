@@ -46,16 +46,15 @@ def _padded(x, m):
 
 def fprop(x, w_lp, m, want_stats: bool = False):
     """x: bf16 NHWC-storage [N,C,H,W]; w_lp: bf16 [K,C,R,S] channels_last (KRSC storage). → y bf16.
-    With ``want_stats`` returns ``(y, sums)`` where sums is [2, K] fp32 (Σy, Σy² per channel, produced by the
-    conv epilogue) or None when the path taken cannot produce them."""
+    With ``want_stats`` returns ``(y, partials)`` where partials is [rows, 2, K] fp32 (per-CTA Σy, Σy² per
+    channel, produced by the conv epilogue) or None when the path taken cannot produce them."""
     md = mode()
     if md != "cudnn":
         u = _umma()
         if u.supports_fprop(x, w_lp, m):
             path_counts["fprop_umma"] += 1
             if want_stats:
-                y, part = u.fprop(x, w_lp, m, want_stats=True)
-                return y, u.stats_reduce(part)
+                return u.fprop(x, w_lp, m, want_stats=True)     # (y, [rows,2,K] partial sums)
             return u.fprop(x, w_lp, m)
         if md == "umma":
             raise RuntimeError(f"B200_CONV=umma but fprop does not cover {m.extra_repr()}")

@@ -65,7 +65,8 @@ int b200_bn_stats(const b200_bf16* x, int64_t rows, int32_t c, const float* gamm
  * library until the process exits. Same inputs, outputs and results as b200_bn_stats, minus the scratch argument.
  * This entry point has no counterpart in the reference.
  *  - Sizes whose scratch need (b200_bn_stats_scratch_bytes) exceeds the array are rejected with -1 and a message in
- *    b200_last_error(): 2 MiB covers any row count up to c = 512 and larger c when rows are few.
+ *    b200_last_error(). The present kernel geometry needs at most ~0.6 MiB for any shape up to c = 4096, so every
+ *    BatchNorm layer of the model zoo fits; the check guards larger channel counts and future geometries.
  *  - The first call on each device looks up the array's device address (with that device current); make that
  *    first call before starting any stream capture.
  *  - All calls on a device share the one array: two calls that may run on the GPU at the same time (different
@@ -81,6 +82,11 @@ int64_t b200_bn_stats_noalloc_max_bytes(void);
 int b200_bn_finalize(const float* sums, int64_t rows, int32_t c, const float* gamma, const float* beta,
                      float* running_mean, float* running_var, float decay, float eps, float* mean, float* rstd,
                      float* scale, float* shift, void* stream);
+
+/* The same, from [nrows][2][c] partial sums as written by b200_conv_fprop (folded here in row order). */
+int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows, int32_t c, const float* gamma,
+                              const float* beta, float* running_mean, float* running_var, float decay, float eps,
+                              float* mean, float* rstd, float* scale, float* shift, void* stream);
 
 /* z = act(scale*x + shift (+ residual)); relu != 0 applies max(0, .). residual may be NULL. In place allowed. */
 int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, int64_t rows, int32_t c,

@@ -32,8 +32,8 @@ int b200_conv_supported(const b200_conv_geom* g, int op);
 
 /* y[n,p,q,k] = sum_{r,s,c} x[n, p*sh - pad_t + r, q*sw - pad_l + s, c] * w[k,r,s,c].
  * col_stats (optional): [b200_conv_stats_rows(g)][2][k] fp32 partial column sums and sums of squares of the
- * stored (bf16-rounded) outputs, one row per 32 output rows group — the batch-norm statistics, produced by the
- * epilogue so that y is not read again. */
+ * stored (bf16-rounded) outputs, one row per (CTA, 32-row group) — the batch-norm statistics, produced by the
+ * epilogue so that y is not read again. The buffer is zeroed by the call; fold it with b200_bn_finalize_partials. */
 int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
                     void* stream);
 int64_t b200_conv_stats_rows(const b200_conv_geom* g);
