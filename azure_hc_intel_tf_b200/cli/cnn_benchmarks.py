@@ -124,7 +124,36 @@ class BenchmarkCNN:
 
     def step(self):
         images, labels = self.data.next()
+        if self.p.use_cuda_graph and self.device.type == "cuda":
+            return self._graph_step(images, labels)
         return self.train_step(images, labels)
+
+    # ------------------------------------------------------------------ whole-step CUDA graph
+    def _graph_step(self, images, labels):
+        """Replay the captured step (forward, backward, fused gradient exchange and update: every launch of the
+        step, including the side-stream collectives) with this step's batch. The first call runs three eager steps
+        (lazy initialisation, plan handshake, allocator warm-up) and then captures. Learning rate and other launch
+        scalars are baked into the graph; changing them needs a re-capture (``self._graph = None``)."""
+        if self._graph is None:
+            self._g_images = images.clone(memory_format=torch.preserve_format)
+            self._g_labels = labels.clone()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    self.train_step(self._g_images, self._g_labels)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._g_loss = self.train_step(self._g_images, self._g_labels)
+            self._graph = g
+        if images.data_ptr() != self._g_images.data_ptr():
+            self._g_images.copy_(images, non_blocking=True)
+            self._g_labels.copy_(labels, non_blocking=True)
+        self._graph.replay()
+        self.global_step += 1
+        return self._g_loss
 
     # ------------------------------------------------------------------ reporting
     def print_info(self):

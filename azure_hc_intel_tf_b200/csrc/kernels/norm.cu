@@ -15,7 +15,8 @@ namespace b200 {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kTargetBlocks = 8 * kNumSMs;   // enough CTAs for ~8 per SM: the passes are latency/bandwidth bound
+constexpr int kTargetBlocks = 8 * kNumSMs;   // elementwise passes: ~8 CTAs per SM
+constexpr int kReduceBlocks = 2 * kNumSMs;   // column reductions: one wave of 2 CTAs per SM keeps the final fold short
 constexpr int kScratchHeader = 64;           // floats reserved in front of the partials (one ticket per channel chunk)
 
 struct ColGeom {
@@ -32,8 +33,8 @@ inline ColGeom col_geom(int64_t rows, int c) {
   g.tx = g.cvecs < 8 ? g.cvecs : 8;
   g.ty = kThreads / g.tx;
   g.ychunks = (g.cvecs + g.tx - 1) / g.tx;
-  int64_t b = (rows + (int64_t)g.ty * 4 - 1) / ((int64_t)g.ty * 4);
-  int cap = kTargetBlocks / g.ychunks;
+  int64_t b = (rows + (int64_t)g.ty * 8 - 1) / ((int64_t)g.ty * 8);
+  int cap = kReduceBlocks / g.ychunks;
   if (cap < 1) cap = 1;
   g.blocks = (int)(b < 1 ? 1 : (b > cap ? cap : b));
   return g;
@@ -172,12 +173,10 @@ __global__ void __launch_bounds__(kThreads, 2) col_reduce_kernel(Policy pol, int
     pol.prepare(cv);
     const int64_t stride = (int64_t)gridDim.x * g.ty;
     int64_t r = (int64_t)blockIdx.x * g.ty + ty;
-    // four rows per trip: four independent groups of 16-byte loads in flight per thread
-    for (; r + 3 * stride < rows; r += 4 * stride) {
-      pol.load(r, cv, a, b);
-      pol.load(r + stride, cv, a, b);
-      pol.load(r + 2 * stride, cv, a, b);
-      pol.load(r + 3 * stride, cv, a, b);
+    // eight rows per trip: eight independent groups of 16-byte loads in flight per thread
+    for (; r + 7 * stride < rows; r += 8 * stride) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) pol.load(r + u * stride, cv, a, b);
     }
     for (; r < rows; r += stride) pol.load(r, cv, a, b);
   }

@@ -269,6 +269,7 @@ class DistributedOptimizer:
         self._cuda = self.grad.is_cuda
         self._comm_stream = torch.cuda.Stream(priority=-1) if self._cuda else None
         self._handles = []
+        self._comm_used = False      # the side stream holds work the compute stream has not joined yet
         self._launched = set()
         self._counts = [0] * len(self.params)
         self._direct_seen = [False] * len(self.params)
@@ -332,6 +333,7 @@ class DistributedOptimizer:
             return
         if self._cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream())
+            self._comm_used = True
         if self.fused and self._symm is not None:
             with torch.cuda.stream(self._comm_stream):
                 if self._opt.lars:
@@ -371,7 +373,8 @@ class DistributedOptimizer:
                 pending_update.append((b, scale))
             self.tracker.done(b)
         if self.fused:
-            stream_ctx = torch.cuda.stream(self._comm_stream) if self._cuda else _null()
+            on_side = self._cuda and self._comm_used
+            stream_ctx = torch.cuda.stream(self._comm_stream) if on_side else _null()
             with stream_ctx:
                 if self._opt.lars:
                     scale = 1.0 / (self.world * self.passes) if self.op == "average" else 1.0 / self.passes
@@ -390,8 +393,10 @@ class DistributedOptimizer:
                             self.grad[lo:hi].mul_(scale)
                     else:
                         self.grad[lo:hi].mul_(scale)
-        if self._cuda:
+        if self._cuda and self._comm_used:
+            # join the side stream (inside a CUDA-graph capture this is the join of the fork made in _launch)
             torch.cuda.current_stream().wait_stream(self._comm_stream)
+            self._comm_used = False
         self._handles = []
 
     def step(self, closure=None):
@@ -409,8 +414,9 @@ class DistributedOptimizer:
 
     def zero_grad(self, set_to_none: bool = False):
         # gradients are views into the fusion buffer: never detach them, just clear the buffer
-        if self._cuda and self._comm_stream is not None:
+        if self._cuda and self._comm_used:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
+            self._comm_used = False
         self.grad.zero_()
 
     @property

@@ -108,6 +108,8 @@ def main() -> int:
     ap.add_argument("--kernels", default=None)
     ap.add_argument("--optimizer", default="momentum")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
+                    help="capture the whole training step in a CUDA graph (auto: on for the b200 arm)")
     a = ap.parse_args()
     if a.impl == "reference":
         return reference_arm()
@@ -132,12 +134,23 @@ def main() -> int:
     argv = [f"--model={a.model}", f"--batch_size={a.batch}", f"--num_batches={a.steps}",
             f"--num_warmup_batches={a.warmup}", "--variable_update=horovod", f"--optimizer={a.optimizer}",
             "--device=gpu", f"--kernels={kernels}", f"--fabric={fabric}", "--use_fp16=True"]
+    use_graph = a.cuda_graph == "on" or (a.cuda_graph == "auto" and a.impl == "b200")
+    argv.append(f"--use_cuda_graph={use_graph}")
 
     def measure(source: str, read_loss: bool):
         """Returns (seconds for K steps on this rank, launches of our kernels, last loss, bench)."""
         p = flags.parse(argv)
         b = BenchmarkCNN(p, data_source=source)
         from azure_hc_intel_tf_b200.ops import b200 as b200ops
+        launches_per_step = None
+        if use_graph:
+            # the first graph-mode call runs eager steps and captures; count our launches in one eager step first
+            b.p.use_cuda_graph = False
+            b.step()
+            b200ops.launch_count = 0
+            b.step()
+            launches_per_step = b200ops.launch_count
+            b.p.use_cuda_graph = True
         for _ in range(a.warmup):
             loss = b.step()
             if read_loss:
@@ -164,7 +177,7 @@ def main() -> int:
         secs = e0.elapsed_time(e1) / 1e3
         if not read_loss:
             last = float(loss.item())
-        launches = b200ops.launch_count
+        launches = b200ops.launch_count if launches_per_step is None else launches_per_step * a.steps
         t = torch.tensor([secs, wall], dtype=torch.float64, device="cuda")
         if n > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -204,7 +217,7 @@ def main() -> int:
                "config": {"model": a.model, "global_batch": global_batch, "per_gpu_batch": a.batch,
                           "image_size": 224 if "inception" not in a.model else 299, "num_classes": 1001,
                           "optimizer": a.optimizer, "parallelism": f"dp{n}", "fabric": fabric_used,
-                          "kernels": kernels_used, "conv_paths": paths,
+                          "kernels": kernels_used, "conv_paths": paths, "cuda_graph": bool(use_graph),
                           "l2": "no flush: each step streams >10 GB of activations, far larger than the 126 MB L2",
                           "timing": "CUDA events on the compute stream, barrier+synchronize both sides, max over ranks"},
                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": loss_v}
