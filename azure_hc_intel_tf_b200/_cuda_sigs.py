@@ -20,6 +20,7 @@ SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_sgd_momentum_flat": (i32, [vp, vp, vp, vp, i64, vp, vp, vp, vp, f32, f32, f32, f32, vp]),
     "b200_lars_norms": (i32, [vp, vp, i64, vp, vp, f32, vp]),
+    "b200_lars_trust_det": (i32, [vp, vp, i64, vp, vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, vp]),
     "b200_lars_trust": (i32, [vp, vp, vp, vp, i32, f32, f32, f32, vp]),
     "b200_bn_stats_scratch_bytes": (i64, [i64, i32]),
     "b200_bn_stats": (i32, [vp, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp, vp]),

@@ -90,6 +90,74 @@ __global__ void lars_trust_kernel(const float* __restrict__ norms, const float* 
   trust[t] = r;
 }
 
+// Deterministic LARS norms: (1) one (sum w^2, sum g^2) pair per 1024-element block, reduced by a fixed tree;
+// (2) one CTA per tensor folds that tensor's blocks in a fixed pattern and writes the trust ratio. Identical inputs
+// give bitwise identical trust ratios on every rank, which keeps data-parallel replicas bit-identical.
+__global__ void __launch_bounds__(256) lars_block_norms_kernel(const float* __restrict__ w, const float* __restrict__ g,
+                                                               int64_t nblk, float* __restrict__ partials, float gscale) {
+  __shared__ float red[2][8];
+  for (int64_t b = blockIdx.x; b < nblk; b += gridDim.x) {
+    int64_t i = b * 1024 + threadIdx.x * 4;
+    float4 wv = *reinterpret_cast<const float4*>(w + i);
+    float4 gv = *reinterpret_cast<const float4*>(g + i);
+    float sw = wv.x * wv.x + wv.y * wv.y + wv.z * wv.z + wv.w * wv.w;
+    float sg = (gv.x * gv.x + gv.y * gv.y + gv.z * gv.z + gv.w * gv.w) * gscale * gscale;
+    sw = warp_sum(sw);
+    sg = warp_sum(sg);
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+      red[0][warp] = sw;
+      red[1][warp] = sg;
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      float s = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[threadIdx.x][k];
+      partials[2 * b + threadIdx.x] = s;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) lars_fold_trust_kernel(const float* __restrict__ partials,
+                                                              const int32_t* __restrict__ blk_lo,
+                                                              const int32_t* __restrict__ blk_cnt,
+                                                              const float* __restrict__ tdecay,
+                                                              const float* __restrict__ tlars, float* __restrict__ trust,
+                                                              float eta, float wd, float eps) {
+  __shared__ float red[2][8];
+  const int t = blockIdx.x;
+  const int lo = blk_lo[t], cnt = blk_cnt[t];
+  float sw = 0.0f, sg = 0.0f;
+  for (int b = threadIdx.x; b < cnt; b += 256) {
+    sw += partials[2 * (lo + b)];
+    sg += partials[2 * (lo + b) + 1];
+  }
+  sw = warp_sum(sw);
+  sg = warp_sum(sg);
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    red[0][warp] = sw;
+    red[1][warp] = sg;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.0f, b2 = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      a += red[0][k];
+      b2 += red[1][k];
+    }
+    float r = 1.0f;
+    if (tlars[t] != 0.0f) {
+      float wn = sqrtf(a), gn = sqrtf(b2);
+      if (wn > 0.0f && gn > 0.0f) r = eta * wn / (gn + wd * tdecay[t] * wn + eps);
+    }
+    trust[t] = r;
+  }
+}
+
 }  // namespace
 }  // namespace b200
 
@@ -121,6 +189,24 @@ int b200_lars_norms(const float* master, const float* grad, int64_t n, const int
   int grid = (int)(nblk < (int64_t)kNumSMs * 8 ? nblk : (int64_t)kNumSMs * 8);
   lars_norms_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(master, grad, nblk, block_tensor, norms,
                                                                         grad_scale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_lars_trust_det(const float* master, const float* grad, int64_t n, float* block_partials,
+                        const int32_t* tensor_blk_lo, const int32_t* tensor_blk_cnt, const float* tensor_decay,
+                        const float* tensor_lars, float* trust, int32_t num_tensors, float eta, float wd, float eps,
+                        float grad_scale, void* stream) {
+  B200_CHECK_ARG(master && grad && block_partials && tensor_blk_lo && tensor_blk_cnt && tensor_decay && tensor_lars && trust,
+                 "lars_trust_det: null pointer");
+  B200_CHECK_ARG(n > 0 && n % 1024 == 0 && num_tensors > 0, "lars_trust_det: n must be a positive multiple of 1024");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int64_t nblk = n / 1024;
+  int grid = (int)(nblk < (int64_t)kNumSMs * 8 ? nblk : (int64_t)kNumSMs * 8);
+  lars_block_norms_kernel<<<grid, 256, 0, st>>>(master, grad, nblk, block_partials, grad_scale);
+  B200_LAUNCH_CHECK();
+  lars_fold_trust_kernel<<<num_tensors, 256, 0, st>>>(block_partials, tensor_blk_lo, tensor_blk_cnt, tensor_decay,
+                                                      tensor_lars, trust, eta, wd, eps);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -18,8 +18,14 @@ def sgd_update(opt, lo: int, hi: int, lr: float, mu: float, wd: float, grad_scal
 
 
 def lars_trust(opt, wd: float, grad_scale: float):
-    opt.norms.zero_()
-    _check(lib().b200_lars_norms(_ptr(opt.master), _ptr(opt.grad), opt.total, _ptr(opt.block_tensor), _ptr(opt.norms),
-                                 grad_scale, _stream()), "lars_norms")
-    _check(lib().b200_lars_trust(_ptr(opt.norms), _ptr(opt.tensor_decay), _ptr(opt.tensor_lars), _ptr(opt.trust),
-                                 len(opt.flags), opt.lars_eta, wd, opt.lars_eps, _stream()), "lars_trust")
+    import torch
+    if not hasattr(opt, "_lars_blk"):
+        lo = torch.tensor([s // 1024 for s, _ in opt.ranges], dtype=torch.int32, device=opt.device)
+        cnt = torch.tensor([(n + 1023) // 1024 for _, n in opt.ranges], dtype=torch.int32, device=opt.device)
+        part = torch.empty(2 * (opt.total // 1024), dtype=torch.float32, device=opt.device)
+        opt._lars_blk = (lo, cnt, part)
+    lo, cnt, part = opt._lars_blk
+    _check(lib().b200_lars_trust_det(_ptr(opt.master), _ptr(opt.grad), opt.total, _ptr(part), _ptr(lo), _ptr(cnt),
+                                     _ptr(opt.tensor_decay), _ptr(opt.tensor_lars), _ptr(opt.trust), len(opt.flags),
+                                     opt.lars_eta, wd, opt.lars_eps, grad_scale, _stream()), "lars_trust_det")
+    b200.count_launch(1)

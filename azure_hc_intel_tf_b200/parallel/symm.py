@@ -1,0 +1,230 @@
+"""Symmetric (peer-mapped) device memory and the NVLink collectives built on it.
+
+Role in the reference stack: MPI_Init / communicator set-up and the UCX (`rc_x,sm,self`) or libfabric transport
+selected by the launcher's fabric argument (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:85-95) — here the
+"transport" is direct load/store into every peer GPU's memory over NVLink 5 / NVSwitch.
+
+Every rank allocates buffers of identical size, exports CUDA IPC handles, and all ranks exchange them once through
+``torch.distributed`` (any backend). Kernels then receive the table of peer addresses (``b200_comm``) and read /
+write the peers directly (csrc/comm/allreduce.cu, include/b200comm.h). ``torch.distributed`` is used for this
+rendezvous only — never for a gradient.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+
+MAX_RANKS = 8
+
+
+class CommStruct(C.Structure):
+    _fields_ = [("buf", C.c_uint64 * MAX_RANKS), ("pad", C.c_uint64 * MAX_RANKS), ("rank", C.c_int32),
+                ("world", C.c_int32), ("ctas", C.c_int32), ("one_shot_max_bytes", C.c_int32)]
+
+
+class SgdArgs(C.Structure):
+    _fields_ = [("master", C.c_void_p), ("mom", C.c_void_p), ("shadow", C.c_void_p), ("block_tensor", C.c_void_p),
+                ("tensor_decay", C.c_void_p), ("tensor_lars", C.c_void_p), ("trust", C.c_void_p),
+                ("lr", C.c_float), ("mu", C.c_float), ("wd", C.c_float)]
+
+
+class _DevArray:
+    """Exposes a raw device allocation to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed ({rc}): {_native.cuda().b200_last_error().decode()}")
+
+
+def _declare(lib):
+    if getattr(lib, "_b200comm_declared", False):
+        return
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.b200_symm_alloc.argtypes, lib.b200_symm_alloc.restype = [i64, C.POINTER(vp)], i32
+    lib.b200_symm_free.argtypes, lib.b200_symm_free.restype = [vp], i32
+    lib.b200_symm_get_handle.argtypes, lib.b200_symm_get_handle.restype = [vp, vp], i32
+    lib.b200_symm_open_handle.argtypes, lib.b200_symm_open_handle.restype = [vp, C.POINTER(vp)], i32
+    lib.b200_symm_close_handle.argtypes, lib.b200_symm_close_handle.restype = [vp], i32
+    lib.b200_comm_pad_bytes.argtypes, lib.b200_comm_pad_bytes.restype = [], i64
+    lib.b200_allreduce_f32.argtypes = [C.POINTER(CommStruct), i64, i64, C.c_float, C.POINTER(SgdArgs), vp]
+    lib.b200_allreduce_f32.restype = i32
+    lib.b200_allreduce_bf16.argtypes = [C.POINTER(CommStruct), i64, i64, C.c_float, vp]
+    lib.b200_allreduce_bf16.restype = i32
+    lib.b200_comm_barrier.argtypes, lib.b200_comm_barrier.restype = [C.POINTER(CommStruct), vp], i32
+    lib.b200_broadcast_f32.argtypes = [C.POINTER(CommStruct), i64, i64, i32, vp]
+    lib.b200_broadcast_f32.restype = i32
+    lib._b200comm_declared = True
+
+
+class SymmBuffer:
+    """One symmetric allocation: ``local`` is this rank's tensor, ``peers[r]`` the device address of rank r's."""
+
+    def __init__(self, ctx: "SymmetricContext", nbytes: int, dtype: torch.dtype):
+        lib = ctx.lib
+        self.ctx = ctx
+        self.nbytes = nbytes
+        ptr = C.c_void_p()
+        _check(lib.b200_symm_alloc(nbytes, C.byref(ptr)), "symm_alloc")
+        self.ptr = ptr.value
+        handle = (C.c_ubyte * 64)()
+        _check(lib.b200_symm_get_handle(C.c_void_p(self.ptr), handle), "symm_get_handle")
+        mine = torch.tensor(list(handle), dtype=torch.uint8)
+        gathered = ctx.all_gather_bytes(mine)
+        self.peers: List[int] = []
+        self._opened: List[int] = []
+        for r in range(ctx.world):
+            if r == ctx.rank:
+                self.peers.append(self.ptr)
+                continue
+            h = (C.c_ubyte * 64)(*gathered[r].tolist())
+            pp = C.c_void_p()
+            _check(lib.b200_symm_open_handle(h, C.byref(pp)), f"symm_open_handle(rank {r})")
+            self.peers.append(pp.value)
+            self._opened.append(pp.value)
+        self._keep = _DevArray(self.ptr, nbytes)
+        self.local_bytes = torch.as_tensor(self._keep, device=ctx.device)
+        self.local = self.local_bytes.view(dtype)
+
+    def close(self):
+        lib = self.ctx.lib
+        for p in self._opened:
+            lib.b200_symm_close_handle(C.c_void_p(p))
+        self._opened = []
+        if self.ptr:
+            lib.b200_symm_free(C.c_void_p(self.ptr))
+            self.ptr = 0
+
+
+class SymmetricContext:
+    def __init__(self, rank: int, world: int, device: torch.device):
+        if world > MAX_RANKS:
+            raise ValueError(f"the NVLink fabric supports up to {MAX_RANKS} ranks on one box, got {world}")
+        self.rank, self.world, self.device = rank, world, device
+        self.lib = _native.cuda()
+        _declare(self.lib)
+        self.ctas = int(os.environ.get("B200_COMM_CTAS", "48"))
+        self.buffers: List[SymmBuffer] = []
+        self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
+        self._scratch: Optional[SymmBuffer] = None
+        self.launches = 0
+        dist.barrier()
+
+    @staticmethod
+    def create(rank, world, device) -> "SymmetricContext":
+        return SymmetricContext(rank, world, device)
+
+    # -- rendezvous helper (works with nccl and gloo process groups)
+    def all_gather_bytes(self, t: torch.Tensor) -> List[torch.Tensor]:
+        backend = dist.get_backend()
+        src = t.to(self.device) if backend == "nccl" else t
+        outs = [torch.empty_like(src) for _ in range(self.world)]
+        dist.all_gather(outs, src)
+        return [o.cpu() for o in outs]
+
+    def alloc(self, nbytes: int, dtype: torch.dtype) -> SymmBuffer:
+        b = SymmBuffer(self, nbytes, dtype)
+        self.buffers.append(b)
+        dist.barrier()           # every rank has mapped every peer before anyone launches a kernel on it
+        return b
+
+    def alloc_like_flat(self, numel: int, dtype: torch.dtype) -> SymmBuffer:
+        return self.alloc(numel * torch.empty((), dtype=dtype).element_size(), dtype)
+
+    def comm_struct(self, buf: SymmBuffer) -> CommStruct:
+        cs = CommStruct()
+        for r in range(self.world):
+            cs.buf[r] = buf.peers[r]
+            cs.pad[r] = self.pad.peers[r]
+        cs.rank, cs.world, cs.ctas, cs.one_shot_max_bytes = self.rank, self.world, self.ctas, 0
+        return cs
+
+    @staticmethod
+    def _stream():
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    # -- collectives on symmetric buffers
+    def allreduce_range_(self, buf: SymmBuffer, lo: int, hi: int, scale: float = 1.0):
+        """In-place sum (times scale) of fp32 elements [lo, hi) of ``buf`` across ranks."""
+        cs = self.comm_struct(buf)
+        if buf.local.dtype == torch.float32:
+            _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, None, self._stream()), "allreduce_f32")
+        elif buf.local.dtype == torch.bfloat16:
+            _check(self.lib.b200_allreduce_bf16(C.byref(cs), lo, hi - lo, scale, self._stream()), "allreduce_bf16")
+        else:
+            raise TypeError(buf.local.dtype)
+        self._count()
+
+    def fused_allreduce_sgd(self, buf: SymmBuffer, opt, lo: int, hi: int, scale: float):
+        """One launch: allreduce [lo, hi) of the symmetric gradient buffer, 1/N scale, momentum-SGD update of
+        ``opt``'s local master / momentum / bf16 weights."""
+        g = opt.param_groups[0]
+        a = SgdArgs(opt.master.data_ptr(), opt.mom.data_ptr(), opt.shadow.data_ptr() if opt.shadow is not None else None,
+                    opt.block_tensor.data_ptr(), opt.tensor_decay.data_ptr(), opt.tensor_lars.data_ptr(),
+                    opt.trust.data_ptr() if opt.lars else None, g["lr"], g["momentum"], g["weight_decay"])
+        cs = self.comm_struct(buf)
+        _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, C.byref(a), self._stream()),
+               "fused allreduce+sgd")
+        self._count()
+
+    def barrier(self):
+        cs = self.comm_struct(self.pad)
+        _check(self.lib.b200_comm_barrier(C.byref(cs), self._stream()), "comm_barrier")
+        self._count()
+
+    def broadcast_(self, buf: SymmBuffer, lo: int, hi: int, root: int):
+        cs = self.comm_struct(buf)
+        _check(self.lib.b200_broadcast_f32(C.byref(cs), lo, hi - lo, root, self._stream()), "broadcast_f32")
+        self._count()
+
+    def allreduce_(self, tensor: torch.Tensor, scale: float = 1.0):
+        """Allreduce an arbitrary CUDA tensor (fp32 / bf16) by staging it through a symmetric scratch buffer.
+        Convenience path for hvd.allreduce(); the gradient path never stages."""
+        flat = tensor.reshape(-1)
+        esz = flat.element_size()
+        gran = 1024 if flat.dtype == torch.float32 else 2048
+        n = (flat.numel() + gran - 1) // gran * gran
+        need = n * 4
+        if self._scratch is None or self._scratch.nbytes < need:
+            # sized collectively: every rank reaches this branch for the same call
+            self._scratch = self.alloc(max(need, 64 << 20), torch.uint8)
+        view = self._scratch.local_bytes[: n * esz].view(flat.dtype)
+        view[: flat.numel()].copy_(flat)
+        if n > flat.numel():
+            view[flat.numel():].zero_()
+        cs = self.comm_struct(self._scratch)
+        if flat.dtype == torch.float32:
+            _check(self.lib.b200_allreduce_f32(C.byref(cs), 0, n, scale, None, self._stream()), "allreduce_f32")
+        else:
+            _check(self.lib.b200_allreduce_bf16(C.byref(cs), 0, n, scale, self._stream()), "allreduce_bf16")
+        self._count()
+        flat.copy_(view[: flat.numel()])
+        return tensor
+
+    def _count(self):
+        self.launches += 1
+        try:
+            from ..ops import b200
+            b200.count_launch(1)
+        except Exception:
+            pass
+
+    def close(self):
+        try:
+            torch.cuda.synchronize()
+        except Exception:
+            pass
+        for b in self.buffers:
+            b.close()
+        self.buffers = []
+        self.pad.close()

@@ -102,3 +102,88 @@ def w_cli(rank, world, argv):
     out = b.run()
     first = next(iter(b.model.parameters())).detach().float().cpu().sum().item()
     return out["images_per_sec"], first
+
+
+# ------------------------------------------------------------------------------------ NVLink fabric (GPU)
+
+def w_nvl_allreduce(rank, world, sizes, iters):
+    """Own P2P allreduce kernels vs the arithmetic answer and vs NCCL, many sizes, repeated (flag-protocol stress)."""
+    import torch.distributed as dist
+    from .. import hvd
+    ctx = hvd.symmetric_context()
+    assert ctx is not None and hvd.fabric() == "nvl"
+    dev = hvd.device()
+    out = []
+    for dtype, gran in ((torch.float32, 1024), (torch.bfloat16, 2048)):
+        nmax = max(sizes)
+        buf = ctx.alloc_like_flat(nmax, dtype)
+        for n in sizes:
+            n = (n + gran - 1) // gran * gran
+            g = torch.Generator(device="cpu").manual_seed(1000 * rank + n % 997)
+            for it in range(iters):
+                x = torch.randn(n, generator=g).to(dev).to(dtype)
+                ref = x.clone().float()
+                dist.all_reduce(ref)                                  # NCCL, fp32 accumulate
+                buf.local[:n].copy_(x)
+                torch.cuda.synchronize()
+                dist.barrier()
+                ctx.allreduce_range_(buf, 0, n, 0.5)
+                torch.cuda.synchronize()
+                got = buf.local[:n].float()
+                tol = 1e-6 if dtype == torch.float32 else 2e-2
+                ok = torch.allclose(got, ref * 0.5, atol=tol * max(1.0, ref.abs().max().item()), rtol=tol)
+                # all ranks must hold bitwise identical results
+                chk = got.double().sum().reshape(1)
+                lo, hi = chk.clone(), chk.clone()
+                dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+                dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+                out.append((str(dtype), n, bool(ok), bool(lo.item() == hi.item())))
+    # back-to-back launches without host synchronisation in between (epochs must keep the ranks in step)
+    buf = ctx.alloc_like_flat(1 << 20, torch.float32)
+    buf.local.fill_(float(rank + 1))
+    torch.cuda.synchronize()
+    dist.barrier()
+    for _ in range(200):
+        ctx.allreduce_range_(buf, 0, 1 << 20, 1.0 / world)
+    torch.cuda.synchronize()
+    expect = sum(range(1, world + 1)) / world
+    out.append(("chain", 1 << 20, bool(torch.allclose(buf.local, torch.full_like(buf.local, expect), rtol=1e-5)), True))
+    # hvd.allreduce on an ordinary tensor (staged through symmetric scratch) and the broadcast kernel
+    t = torch.arange(5000, device=dev, dtype=torch.float32) * (rank + 1)
+    s = hvd.allreduce(t, op=hvd.Sum)
+    out.append(("staged", 5000, bool(torch.allclose(s, torch.arange(5000, device=dev) * float(sum(range(1, world + 1))))), True))
+    b = ctx.alloc_like_flat(4096, torch.float32)
+    b.local.fill_(float(rank))
+    torch.cuda.synchronize()
+    dist.barrier()
+    ctx.broadcast_(b, 0, 4096, world - 1)
+    torch.cuda.synchronize()
+    out.append(("bcast", 4096, bool((b.local == float(world - 1)).all().item()), True))
+    return out
+
+
+def w_nvl_fused_training(rank, world, steps, lars):
+    """DistributedOptimizer on the nvl fabric (fused allreduce+SGD kernel) vs a single-process run on the
+    concatenated batch; also returns whether ranks ended bit-identical."""
+    from .. import hvd
+    dev = hvd.device()
+    net = _net(dev)
+    named = list(net.named_parameters())
+    mk = hvd.LARS if lars else hvd.MomentumSGD
+    kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-3, fusion_threshold=8192)
+    if lars:
+        kw["eta"] = 0.01
+    opt = hvd.DistributedOptimizer(mk(named, **kw), named_parameters=named)
+    hvd.broadcast_parameters(net.state_dict(), root_rank=0)
+    hvd.broadcast_optimizer_state(opt, root_rank=0)
+    g = torch.Generator().manual_seed(7)
+    full_x = torch.randn(steps, 4 * world, 3, 8, 8, generator=g)
+    full_y = torch.randn(steps, 4 * world, 10, generator=g)
+    for s in range(steps):
+        x = full_x[s, rank * 4:(rank + 1) * 4].to(dev)
+        y = full_y[s, rank * 4:(rank + 1) * 4].to(dev)
+        opt.zero_grad()
+        ((net(x) - y) ** 2).mean().backward()
+        opt.step()
+    torch.cuda.synchronize()
+    return [p.detach().cpu().contiguous() for p in net.parameters()], len(opt.plan.buckets), opt._symm is not None

@@ -45,6 +45,14 @@ int b200_lars_norms(const float* master, const float* grad, int64_t n, const int
 int b200_lars_trust(const float* norms, const float* tensor_decay, const float* tensor_lars, float* trust,
                     int32_t num_tensors, float eta, float wd, float eps, void* stream);
 
+/* Deterministic variant used by the framework: per-1024-block partial norms (block_partials: 2 floats per block)
+ * folded per tensor in a fixed order; tensor t owns blocks [tensor_blk_lo[t], +tensor_blk_cnt[t]). Identical inputs
+ * give bitwise identical trust ratios, so data-parallel replicas stay bit-identical. */
+int b200_lars_trust_det(const float* master, const float* grad, int64_t n, float* block_partials,
+                        const int32_t* tensor_blk_lo, const int32_t* tensor_blk_cnt, const float* tensor_decay,
+                        const float* tensor_lars, float* trust, int32_t num_tensors, float eta, float wd, float eps,
+                        float grad_scale, void* stream);
+
 /* ------------------------------------------------------------------ batch norm (K4/K5; MKL-DNN fused BN) */
 
 /* Bytes of scratch b200_bn_stats needs for a tensor of `rows` x `c`. */

@@ -1,0 +1,41 @@
+"""NVLink fabric: hand-written P2P allreduce / fused allreduce+SGD / broadcast kernels on 2+ GPUs, against the
+arithmetic answer, against NCCL, and against a single-process run (SURVEY.md §4 "GPU" bullet; K-AR1/2/4, K-BC,
+K-BAR). Reference role: Horovod's MPI_Allreduce on the fusion buffer (run-tf-sing-ucx-openmpi.sh:105) + TF
+ApplyMomentum (:73)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+needs2 = pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+
+
+@needs2
+def test_p2p_allreduce_matches_nccl_and_is_rank_consistent():
+    from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
+    world = min(_ngpu(), 8)
+    sizes = [1024, 4096, 100_000, 1 << 20, (1 << 22) + 4096]
+    outs = testing.run_ranks(W.w_nvl_allreduce, world, "nvl", args=(sizes, 3), timeout=600)
+    for rank_out in outs:
+        for dtype, n, ok, same in rank_out:
+            assert ok and same, (dtype, n, ok, same)
+
+
+@needs2
+@pytest.mark.parametrize("lars", [False, True])
+def test_fused_allreduce_sgd_training_matches_single_process(lars):
+    from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
+    world = 2
+    outs = testing.run_ranks(W.w_nvl_fused_training, world, "nvl", args=(4, lars), timeout=600)
+    (w0, nb, used0), (w1, _, used1) = outs
+    assert used0 and used1 and nb > 1
+    for a, b in zip(w0, w1):
+        assert torch.equal(a, b)
+    ref = W.single_process_reference(world, "lars" if lars else "fused", 4)
+    for a, r in zip(w0, ref):
+        assert torch.allclose(a, r, atol=5e-6, rtol=2e-4)
