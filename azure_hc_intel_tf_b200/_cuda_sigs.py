@@ -53,6 +53,9 @@ OPTIONAL = {
     "b200_conv_wgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
     "b200_conv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_gemm_nt": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp]),
+    "b200_gemm_nt_stats": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "b200_gemm_stats_rows": (i64, [i32, i32]),
+    "b200_im2col_small_c": (i32, [vp, vp, C.POINTER(ConvGeom), i32, vp]),
     "b200_gemm_nn": (i32, [vp, i32, vp, vp, i32, i32, i32, vp]),
     "b200_dense_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, vp]),
     "b200_dense_wgrad_workspace_bytes": (i64, [i32, i32, i32]),

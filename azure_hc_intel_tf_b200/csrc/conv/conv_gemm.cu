@@ -576,8 +576,22 @@ int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16*
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 
+int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
+                       int32_t ldo, int32_t out_fp32, float* col_stats, void* stream);
+
 int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
                  int32_t out_fp32, void* stream) {
+  return b200_gemm_nt_stats(a, b, out, m, n, k, ldo, out_fp32, nullptr, stream);
+}
+
+int64_t b200_gemm_stats_rows(int32_t m, int32_t n) {
+  const int bn = pick_block_n(n);
+  int64_t tiles = ((int64_t)m + kBlockM - 1) / kBlockM * ((n + bn - 1) / bn);
+  return (tiles < kNumSMs ? tiles : kNumSMs) * 4;
+}
+
+int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
+                       int32_t ldo, int32_t out_fp32, float* col_stats, void* stream) {
   B200_CHECK_ARG(a && b && out, "gemm_nt: null pointer");
   B200_CHECK_ARG(m > 0 && n > 0 && k > 0 && k % 64 == 0 && ldo >= n, "gemm_nt: need k%%64==0 and ldo>=n");
   CUtensorMap ma, mb;
@@ -595,6 +609,10 @@ int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, i
   p.out = out;
   p.ldo = ldo;
   p.out_fp32 = out_fp32;
+  p.col_stats = col_stats;
+  if (col_stats)
+    B200_CUDA(cudaMemsetAsync(col_stats, 0, sizeof(float) * 2 * (size_t)n * (size_t)b200_gemm_stats_rows(m, n),
+                              static_cast<cudaStream_t>(stream)));
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 

@@ -16,7 +16,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kTargetBlocks = 8 * kNumSMs;   // elementwise passes: ~8 CTAs per SM
-constexpr int kReduceBlocks = 2 * kNumSMs;   // column reductions: one wave of 2 CTAs per SM keeps the final fold short
+constexpr int kReduceBlocks = 3 * kNumSMs;   // column reductions: one wave of 3 CTAs per SM keeps the final fold short
 constexpr int kScratchHeader = 64;           // floats reserved in front of the partials (one ticket per channel chunk)
 
 struct ColGeom {
@@ -87,43 +87,47 @@ struct BwdReducePolicy {
   int relu;
   float *dgamma, *dbeta;
   int c;
-  float k_mean[8], k_rstd[8], k_scale[8], k_shift[8];
+  float k_scale[8], k_shift[8];
 
   __device__ __forceinline__ void prepare(int cv) {
     const int ch = cv * 8;
+    if (relu && !z) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      k_mean[i] = mean[ch + i];
-      k_rstd[i] = rstd[ch + i];
-      k_scale[i] = scale[ch + i];
-      k_shift[i] = shift[ch + i];
+      for (int i = 0; i < 8; ++i) {
+        k_scale[i] = scale[ch + i];
+        k_shift[i] = shift[ch + i];
+      }
     }
   }
+  // accumulates a = sum g and b = sum g*x; dgamma = rstd * (b - mean * a) is formed once per channel in finalize
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float g[8], xv[8];
     const int64_t off = row * c + cv * 8;
-    unpack8(ld8_stream(dz + off), g);
-    unpack8(ld8_stream(x + off), xv);
-    if (relu) {
-      if (z) {
-        float zv[8];
-        unpack8(ld8_stream(z + off), zv);
+    const bf16x8 gq = ld8_stream(dz + off), xq = ld8_stream(x + off);
+    if (relu && z) {
+      float zv[8];
+      unpack8(ld8_stream(z + off), zv);
+      unpack8(gq, g);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
-      } else {
+      for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
+      unpack8(xq, xv);
+    } else {
+      unpack8(gq, g);
+      unpack8(xq, xv);
+      if (relu) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) g[i] = fmaf(k_scale[i], xv[i], k_shift[i]) > 0.0f ? g[i] : 0.0f;
       }
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      a[i] += g[i];                                                    // dbeta
-      b[i] = fmaf(g[i], (xv[i] - k_mean[i]) * k_rstd[i], b[i]);        // dgamma
+      a[i] += g[i];
+      b[i] = fmaf(g[i], xv[i], b[i]);
     }
   }
   __device__ __forceinline__ void finalize(int ch, float s1, float s2) const {
     dbeta[ch] = s1;
-    dgamma[ch] = s2;
+    dgamma[ch] = rstd[ch] * (s2 - mean[ch] * s1);
   }
 };
 
@@ -158,7 +162,7 @@ struct BiasBwdPolicy {
 // ---- skeleton -------------------------------------------------------------------------------------
 
 template <class Policy>
-__global__ void __launch_bounds__(kThreads, 2) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
+__global__ void __launch_bounds__(kThreads, 3) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
                                                                  float* scratch) {
   __shared__ float sm[kThreads * 16];
   __shared__ int is_last;

@@ -154,13 +154,20 @@ class _ConvBlock(torch.autograd.Function):
         w_lp = lowp(weight)
         ctx.m, ctx.relu = m, relu
         ctx.has_res = residual is not None
+        first = conv_impl.first_layer(x, m)       # Cin = 3: explicit patch matrix, kept for the weight gradient
+        ctx.first = first
+        if first:
+            y, sums, patches = conv_impl.first_fprop(x, w_lp, m, m.bn is not None and m.bn.training)
+            x = patches
         if m.bn is not None:
-            y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
+            if not first:
+                y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
             z, stats = bn_forward(y, m.bn, residual, relu, sums)
             # the ReLU mask is recomputed from y when there is no residual, else read from z
             ctx.save_for_backward(x, w_lp, y, z if (relu and residual is not None) else None, stats)
         else:
-            y = conv_impl.fprop(x, w_lp, m)
+            if not first:
+                y = conv_impl.fprop(x, w_lp, m)
             if bias is not None or relu:
                 n, c, h, w = y.shape
                 _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
@@ -195,8 +202,12 @@ class _ConvBlock(torch.autograd.Function):
             else:
                 dy = dz
         g_w = _direct(weight)
-        dw = conv_impl.wgrad(x, dy, m, out=g_w)
-        dx = conv_impl.dgrad(dy, w_lp, m, x.shape) if ctx.needs_input_grad[0] else None
+        if ctx.first:
+            dw = conv_impl.first_wgrad(x, dy, m, out=g_w)      # x holds the saved patch matrix
+            dx = None
+        else:
+            dw = conv_impl.wgrad(x, dy, m, out=g_w)
+            dx = conv_impl.dgrad(dy, w_lp, m, x.shape) if ctx.needs_input_grad[0] else None
         return (dx, _deliver(weight, g_w, dw),
                 _deliver(gamma, g_gamma, dgamma) if (gamma is not None and gamma.requires_grad) else None,
                 _deliver(beta, g_beta, dbeta) if beta is not None else None,

@@ -118,6 +118,23 @@ def wgrad(x, dy, m, out=None):
     return dw.float()
 
 
+# ------------------------------------------------------------------------------------ first layer (Cin = 3)
+
+def first_layer(x, m) -> bool:
+    """True when the small-Cin path (explicit patch matrix + tensor-core GEMM) handles this layer."""
+    return mode() != "cudnn" and m.cin < 8 and not x.requires_grad and _umma().supports_first_layer(x, m)
+
+
+def first_fprop(x, w_lp, m, want_stats):
+    path_counts["fprop_umma_first"] += 1
+    return _umma().first_layer_fprop(x, w_lp, m, want_stats)
+
+
+def first_wgrad(patches, dy, m, out=None):
+    path_counts["wgrad_umma_first"] += 1
+    return _umma().first_layer_wgrad(patches, dy, m, out)
+
+
 # ------------------------------------------------------------------------------------ dense GEMMs
 
 def gemm_nt(a, b, out_fp32: bool = False):

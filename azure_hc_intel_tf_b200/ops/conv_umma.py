@@ -127,3 +127,46 @@ def dense_wgrad(x, dy, out_features, out=None):
            "dense_wgrad")
     b200.count_launch(1 if ws is not None else 0)
     return out
+
+
+# ------------------------------------------------------------------------------------ first layer (Cin = 3)
+
+def supports_first_layer(x, m) -> bool:
+    return "first" not in _disabled and m.cin < 8 and m.cout % 8 == 0 and hasattr(lib(), "b200_im2col_small_c")
+
+
+def first_layer_kpad(m) -> int:
+    return (m.k[0] * m.k[1] * m.cin + 63) // 64 * 64
+
+
+def first_layer_fprop(x, w_lp, m, want_stats: bool):
+    """Explicit im2col (patch matrix A) + tcgen05 GEMM. Returns (y, partial stats or None, A); A is kept for wgrad."""
+    g = geom(x.shape, m)
+    kdim, kpad = m.k[0] * m.k[1] * m.cin, first_layer_kpad(m)
+    rows = g.n * g.p * g.q
+    a = torch.empty((rows, kpad), dtype=_BF16, device=x.device)
+    _check(lib().b200_im2col_small_c(_ptr(x), _ptr(a), C.byref(g), kpad, _stream()), "im2col_small_c")
+    # filter [K, C, R, S] channels_last = KRSC storage = [K, R*S*C] row-major; pad the rows to kpad
+    w2 = torch.zeros((m.cout, kpad), dtype=_BF16, device=x.device)
+    w2[:, :kdim] = w_lp.permute(0, 2, 3, 1).reshape(m.cout, kdim)
+    y = empty_nhwc(g.n, g.k, g.p, g.q, x.device)
+    stats = None
+    if want_stats:
+        srows = lib().b200_gemm_stats_rows(rows, g.k)
+        stats = torch.empty((srows, 2, g.k), dtype=torch.float32, device=x.device)
+    _check(lib().b200_gemm_nt_stats(_ptr(a), _ptr(w2), _ptr(y), rows, g.k, kpad, g.k, 0, _ptr(stats), _stream()),
+           "gemm_nt_stats")
+    return y, stats, a
+
+
+def first_layer_wgrad(a, dy, m, out=None):
+    """dw[K, C, R, S] fp32 from the saved patch matrix: dense_wgrad(A, dY) then drop the K padding."""
+    kdim = m.k[0] * m.k[1] * m.cin
+    n, k, p, q = dy.shape
+    dy2 = dy.permute(0, 2, 3, 1).reshape(n * p * q, k)
+    full = dense_wgrad(a, dy2, k)                                  # [K, kpad] fp32
+    dw = full[:, :kdim].reshape(k, m.k[0], m.k[1], m.cin).permute(0, 3, 1, 2)
+    if out is not None:
+        out.copy_(dw)
+        return out
+    return dw

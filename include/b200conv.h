@@ -52,6 +52,16 @@ int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
 int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
                  int32_t out_fp32, void* stream);
 
+/* b200_gemm_nt that also emits per-column statistics of the stored outputs, like b200_conv_fprop
+ * (col_stats: [b200_gemm_stats_rows(m, n)][2][n] fp32, zeroed by the call). */
+int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
+                       int32_t ldo, int32_t out_fp32, float* col_stats, void* stream);
+int64_t b200_gemm_stats_rows(int32_t m, int32_t n);
+
+/* Patch matrix for small-Cin (first-layer) convolutions: a[n*p*q][kpad] bf16, column (r*S + s)*Cin + c, zero padded
+ * from R*S*Cin up to kpad (a multiple of 64). Forward: gemm_nt(a, w_padded); weight gradient: dense_wgrad(a, dy). */
+int b200_im2col_small_c(const b200_bf16* x, b200_bf16* a, const b200_conv_geom* g, int32_t kpad, void* stream);
+
 /* out[m, n] (bf16) = a[m, k] . b[k, n]; a has leading dimension lda >= k (multiple of 8; elements past k must be
  * zero or lda == k), b is row-major [k][n] and is read in place as an MN-major operand; n % 64 == 0. */
 int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16* out, int32_t m, int32_t n, int32_t k,

@@ -146,3 +146,27 @@ def test_dense_layer_gemms(b, i, o):
         dx = conv_umma.gemm_nn(dy, w, k=o)
         ref_dx = dy[:, :o].float() @ w.float()
         assert rel_err(dx, ref_dx) < 1e-2
+
+
+@pytest.mark.parametrize("n,h,w,cout,k,stride,pad", [
+    (4, 224, 224, 64, 7, 2, ((3, 3), (3, 3))),      # ResNet conv0
+    (2, 224, 224, 64, 3, 1, ((1, 1), (1, 1))),      # VGG conv1_1
+    (2, 299, 299, 32, 3, 2, ((0, 0), (0, 0))),      # Inception-v3 stem
+    (2, 227, 227, 64, 11, 4, ((0, 0), (0, 0))),     # AlexNet
+])
+def test_first_layer_patch_matrix_path(n, h, w, cout, k, stride, pad):
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    m = M(3, cout, k, stride, pad, (h, w))
+    x, wt = rnd((n, h, w, 3), 1), wrnd(cout, 3, m.k[0], m.k[1], 2)
+    assert conv_umma.supports_first_layer(x, m)
+    y, stats, patches = conv_umma.first_layer_fprop(x, wt, m, True)
+    ref = ref_conv(x, wt, m)
+    assert y.shape == ref.shape and rel_err(y, ref) < 1e-2
+    from azure_hc_intel_tf_b200.ops.b200 import lib
+    sums = stats.sum(0)
+    assert torch.allclose(sums[0], y.float().sum((0, 2, 3)), rtol=2e-3, atol=1.0)
+    dy = rnd((n, m.out_hw[0], m.out_hw[1], cout), 3, 0.1)
+    dw = conv_umma.first_layer_wgrad(patches, dy, m)
+    wf = wt.float().requires_grad_()
+    ref_conv(x, wf, m).backward(dy.float())
+    assert dw.shape == wf.grad.shape and rel_err(dw, wf.grad) < 5e-3
