@@ -1,0 +1,22 @@
+"""Runs one convolution layer through the tcgen05 kernels a few times (ncu capture target).
+usage: one_conv.py cin h cout k stride [batch]"""
+import sys
+import torch
+sys.path.insert(0, ".")
+from azure_hc_intel_tf_b200.ops import conv_umma
+cin, h, cout, k, stride = map(int, sys.argv[1:6])
+n = int(sys.argv[6]) if len(sys.argv) > 6 else 256
+class M: pass
+m = M(); m.cin, m.cout, m.k, m.stride = cin, cout, (k, k), (stride, stride)
+pd = (k - 1) // 2
+m.pad = ((pd, pd), (pd, pd)); m.out_hw = ((h + 2 * pd - k) // stride + 1,) * 2
+x = torch.randn(n, h, h, cin, device="cuda").bfloat16().permute(0, 3, 1, 2)
+w = torch.randn(cout, k, k, cin, device="cuda").bfloat16().permute(0, 3, 1, 2)
+dy = torch.randn(n, m.out_hw[0], m.out_hw[1], cout, device="cuda").bfloat16().permute(0, 3, 1, 2)
+for _ in range(3):
+    y, st = conv_umma.fprop(x, w, m, want_stats=True)
+    if conv_umma.supports_dgrad(dy, w, m, x.shape):
+        dx = conv_umma.dgrad(dy, w, m, x.shape)
+    dw = conv_umma.wgrad(x, dy, m)
+torch.cuda.synchronize()
+print("ok", y.shape, dw.shape)
