@@ -146,7 +146,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tma_load_2d(sa, &map_a, &bars->full[stage], kb * kBlockK, m0);
           }
           if (!p.b_mn_major) {
-            tma_load_2d(sb, &map_b, &bars->full[stage], kb * kBlockK, n0);
+            // K-major weights [Cout][(r,s),Cin]: chunk cc of tap (r,s). With Cin % 64 != 0 the last chunk of a tap
+            // runs into the next tap's channels; the matching A columns were zero-filled by TMA, so they add nothing.
+            tma_load_2d(sb, &map_b, &bars->full[stage], p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n0);
           } else {
             // weight row = one output channel (GEMM K index); columns = ((r,s), cin). Taps are flipped.
             const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s);
@@ -223,7 +225,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           uint8_t* buf = out_stage + (box_counter & 1) * kStageOutBytes;
           // this CTA's running column statistics for (row group qtr, column pair cp) of this box: fetched now, the
           // latency hides behind the TMEM loads below; only this thread ever touches these addresses
-          float* const st_dst = p.col_stats
+          float* const st_dst = (p.col_stats && n0 + bx * 64 + cp * 2 < p.N)
                                     ? p.col_stats + ((size_t)blockIdx.x * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
                                     : nullptr;
           float2 old1 = make_float2(0.f, 0.f), old2 = make_float2(0.f, 0.f);
@@ -265,7 +267,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
             tma_store_commit();
           }
-          if (p.col_stats) {
+          if (st_dst) {
             float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
             const int chunk = cp >> 2, word = cp & 3;
 #pragma unroll 8
@@ -396,12 +398,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // ---------------------------------------------------------------------------------------- host side
 
 int pick_block_n(int n) {
-  if (n % 256 == 0) return 256;
-  if (n % 128 == 0) return 128;
-  if (n <= 256 && n % 16 == 0) return n;
-  for (int bn = 256; bn >= 16; bn -= 16)
-    if (n % bn == 0) return bn;
-  return ((n < 256 ? n : 256) + 15) / 16 * 16;   // tail columns are masked in the epilogue
+  // N >= 64: a multiple of 64 (staged TMA-store epilogue); columns past N are zero-filled on load, clipped on store
+  // and skipped in the statistics. Prefer the widest tile that wastes at most a quarter of its columns.
+  if (n >= 64) {
+    const int cand[4] = {256, 192, 128, 64};
+    for (int i = 0; i < 4; ++i) {
+      const int bn = cand[i];
+      const int tiles = (n + bn - 1) / bn;
+      if ((tiles * bn - n) * 4 <= tiles * bn) return bn;
+    }
+    return 64;
+  }
+  return (n + 15) / 16 * 16;   // narrow outputs: one tile, direct-store epilogue masks the tail
 }
 
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStream_t st) {
@@ -446,10 +454,11 @@ int b200_conv_supported(const b200_conv_geom* g, int op) {
   if (g->n <= 0 || g->p <= 0 || g->q <= 0) return 0;
   if (op == B200_CONV_WGRAD) return b200_conv_wgrad_supported(g);
   if (op == B200_CONV_FPROP) {
-    return g->c % 64 == 0 && g->k % 16 == 0 && g->r <= 15 && g->s <= 15;
+    // channel chunks past Cin are zero-filled by TMA, so Cin only has to keep rows 16-byte aligned
+    return g->c >= 64 && g->c % 8 == 0 && g->k % 16 == 0 && g->r <= 15 && g->s <= 15;
   }
   if (op == B200_CONV_DGRAD) {
-    if (g->k % 64 != 0 || g->c % 64 != 0) return 0;
+    if (g->k < 64 || g->c < 64 || g->k % 8 != 0 || g->c % 8 != 0) return 0;
     if (g->stride_h == 1 && g->stride_w == 1) return g->r <= 15 && g->s <= 15;
     // strided: only 1x1 without padding (ResNet v1 down-sampling convolutions)
     return g->r == 1 && g->s == 1 && g->pad_t == 0 && g->pad_l == 0 && g->pad_b == 0 && g->pad_r == 0 &&
@@ -461,7 +470,7 @@ int b200_conv_supported(const b200_conv_geom* g, int op) {
 int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
                     void* stream) {
   B200_CHECK_ARG(x && w && y && g, "conv_fprop: null pointer");
-  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin%%64==0, Cout%%16==0)");
+  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin>=64, Cin%%8==0, Cout%%16==0)");
   CUtensorMap ma, mb;
   const int upper_w = g->pad_r - (g->s - 1), upper_h = g->pad_b - (g->r - 1);
   if (tmap_im2col_nhwc(&ma, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
@@ -475,9 +484,10 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   if (tmap_tiled_2d(&mb, w, 2, (uint64_t)kdim, (uint64_t)g->k, (uint64_t)kdim * 2, kBlockK, p.block_n, true)) return -1;
   p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
   p.num_n_tiles = (p.N + p.block_n - 1) / p.block_n;
-  p.cchunks = g->c / kBlockK;
+  p.cchunks = (g->c + kBlockK - 1) / kBlockK;
   p.num_k_blocks = g->r * g->s * p.cchunks;
   p.a_im2col = 1;
+  p.b_row_len = g->c;
   p.PQ = g->p * g->q;
   p.Q = g->q;
   p.stride_h = g->stride_h;
@@ -534,12 +544,14 @@ int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, cons
   }
   p.stride_h = p.stride_w = 1;
   p.N = g->c;
-  p.block_n = g->c % 256 == 0 ? 256 : (g->c % 128 == 0 ? 128 : 64);
+  // tile width: a multiple of 64 (the MN-major weight boxes are 64 columns wide); columns past Cin are zero-filled on
+  // load and clipped on store
+  p.block_n = g->c % 256 == 0 ? 256 : (g->c % 128 == 0 ? 128 : (g->c % 64 == 0 ? 64 : (g->c > 192 ? 256 : (g->c > 128 ? 192 : 128))));
   const int row = g->r * g->s * g->c;
   if (tmap_tiled_2d(&mb, w, 2, (uint64_t)row, (uint64_t)g->k, (uint64_t)row * 2, 64, kBlockK, true)) return -1;
   p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
-  p.num_n_tiles = p.N / p.block_n;
-  p.cchunks = g->k / kBlockK;
+  p.num_n_tiles = (p.N + p.block_n - 1) / p.block_n;
+  p.cchunks = (g->k + kBlockK - 1) / kBlockK;
   p.num_k_blocks = g->r * g->s * p.cchunks;
   p.a_im2col = 1;
   p.R = g->r;

@@ -33,8 +33,9 @@ constexpr int kTmemCols = 512;
 constexpr int kMaxStages = 6;
 
 struct WgradParams {
-  int rows_total;        // R*S*C  (valid (tap,c) rows)
+  int rows_total;        // R*S*C  (valid (tap,c) rows, = row length of dw)
   int C, S, RS;
+  int Cp;                // C rounded up to 64: the M index space is (tap, c') with c' < Cp; c' >= C is zero padding
   int kout;              // output channels
   int block_n;           // N tile (multiple of 16, <= 256)
   int n_tiles;           // ceil(kout / block_n)
@@ -119,9 +120,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         for (int t = 0; t < tiles_here; ++t) {
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
-            int idx = (tile0 + t) * 128 + half * 64;      // first (tap,c) row of this 64-row chunk
-            int tap = idx / p.C;
-            int c0 = idx - tap * p.C;
+            int idx = (tile0 + t) * 128 + half * 64;      // first (tap,c') row of this 64-row chunk
+            int tap = idx / p.Cp;
+            int c0 = idx - tap * p.Cp;
             if (tap >= p.RS) {                            // past the last tap: load something valid, it is masked
               tap = p.RS - 1;
               c0 = p.C;                                   // fully out of bounds in C -> zero fill
@@ -173,8 +174,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     const size_t ld = (size_t)p.rows_total;       // dw[k][rows_total]
     float* const outp = p.ws ? p.ws + (size_t)slice * p.out_elems : p.dw;
     for (int t = 0; t < tiles_here; ++t) {
-      const int idx = (tile0 + t) * 128 + lane_group * 32 + lane;
-      const bool valid = idx < p.rows_total;
+      const int pidx = (tile0 + t) * 128 + lane_group * 32 + lane;   // position in the padded (tap, c') space
+      const int ptap = pidx / p.Cp, pc = pidx - ptap * p.Cp;
+      const bool valid = ptap < p.RS && pc < p.C;
+      const int idx = ptap * p.C + pc;                                // position in a dw row
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(t * p.block_n);
       for (int c = 0; c < p.block_n; c += 16) {
         uint32_t r[16];
@@ -234,13 +237,14 @@ constexpr int64_t kWorkspaceCap = 96ll << 20;
 
 int plan(const b200_conv_geom* g, WgradParams& p) {
   p.C = g->c;
+  p.Cp = (g->c + 63) / 64 * 64;
   p.S = g->s;
   p.RS = g->r * g->s;
   p.rows_total = p.RS * g->c;
   p.kout = g->k;
   p.block_n = g->k >= 256 ? 256 : (g->k + 15) / 16 * 16;
   p.n_tiles = (g->k + p.block_n - 1) / p.block_n;
-  p.m_tiles_total = (p.rows_total + 127) / 128;
+  p.m_tiles_total = (p.RS * p.Cp + 127) / 128;
   const int nb = (p.block_n + 63) / 64;
   int T = kTmemCols / p.block_n;
   // two pipeline stages must fit in ~200 KiB: (T*16 KiB + nb*8 KiB) * 2
@@ -287,11 +291,11 @@ extern "C" {
 
 int b200_conv_wgrad_supported(const b200_conv_geom* g) {
   if (!g) return 0;
-  return g->c % 64 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0;
+  return g->c >= 64 && g->c % 8 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0;
 }
 
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g) {
-  if (!g || g->c % 64 != 0) return 0;
+  if (!g || g->c < 64 || g->c % 8 != 0) return 0;
   WgradParams p{};
   plan(g, p);
   return p.slices > 1 ? (int64_t)p.slices * p.out_elems * 4 : 0;
@@ -333,8 +337,8 @@ int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t
 static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
                       void* workspace, void* stream) {
   B200_CHECK_ARG(x && dy && dw && g, "conv_wgrad: null pointer");
-  B200_CHECK_ARG(g->c % 64 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
-                 "conv_wgrad: unsupported geometry (need Cin%%64==0, dy row stride %%8==0)");
+  B200_CHECK_ARG(g->c >= 64 && g->c % 8 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
+                 "conv_wgrad: unsupported geometry (need Cin>=64, Cin%%8==0, dy row stride %%8==0)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   WgradParams p{};
   plan(g, p);
