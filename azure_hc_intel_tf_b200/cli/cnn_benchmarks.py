@@ -74,6 +74,8 @@ class BenchmarkCNN:
                         seed=p.seed + self.rank, own_kernels=self.kernels == "b200")
         self._graph = None
         self._last_save = time.time()
+        import os as _os
+        self._nvtx = self.device.type == "cuda" and _os.environ.get("B200_NVTX", "") not in ("", "0")
 
     # ------------------------------------------------------------------ set-up
     def _make_optimizer(self):
@@ -115,10 +117,21 @@ class BenchmarkCNN:
             with torch.no_grad():
                 loss, _ = self.forward_loss(images, labels)
             return loss
+        nvtx = self._nvtx
         self.opt.zero_grad(set_to_none=not hasattr(self.opt, "plan"))
+        if nvtx:
+            torch.cuda.nvtx.range_push("forward")
         loss, _ = self.forward_loss(images, labels)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("backward+allreduce")
         loss.backward()
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("optimizer")
         self.opt.step()
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         self.global_step += 1
         return loss
 
@@ -204,6 +217,8 @@ class BenchmarkCNN:
         self._sync()
         self._barrier()
         self._sync()
+        if p.trace_file and self.rank == 0:
+            self._write_trace(p.trace_file)
         if self.rank == 0:
             print("Done warm up")
             print(log.table_header())
@@ -258,6 +273,20 @@ class BenchmarkCNN:
         if self.timeline is not None:
             self.timeline.close()
         return summary
+
+    def _write_trace(self, path: str):
+        """--trace_file: Chrome trace of one training step (tf_cnn_benchmarks' flag of the same name; the reference
+        does not set it — SURVEY.md §5.1). CPU ops, CUDA kernels and NVTX ranges of exactly one step."""
+        from torch.profiler import ProfilerActivity, profile
+        acts = [ProfilerActivity.CPU] + ([ProfilerActivity.CUDA] if self.device.type == "cuda" else [])
+        was = self._nvtx
+        self._nvtx = self.device.type == "cuda"
+        with profile(activities=acts) as prof:
+            self.step()
+            self._sync()
+        self._nvtx = was
+        prof.export_chrome_trace(path)
+        print(f"Wrote trace of one step to {path}")
 
     def _maybe_save(self):
         p = self.p

@@ -156,6 +156,75 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
 }
 
+// One-shot variant for small messages (one 1024-element block per CTA): every rank reads the block from all peers and
+// reduces it itself in rank order - a single NVLink traversal instead of two. The second barrier keeps a fast rank
+// from overwriting its buffer while a slower peer is still reading it.
+__global__ void __launch_bounds__(kThreads) allreduce_f32_oneshot_kernel(CommDev c, int64_t offset, int64_t nblk,
+                                                                         float scale, SgdDev sgd) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
+  __syncthreads();
+  cta_barrier_all_ranks(c, &s_epoch);
+  const int tid = threadIdx.x;
+  const int64_t b = blockIdx.x;              // grid == nblk
+  const int64_t off = offset + b * 1024 + tid * 4;
+  float4 v[B200_COMM_MAX_RANKS];
+#pragma unroll
+  for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
+    if (p < c.world) v[p] = ld_peer_f4(reinterpret_cast<const float*>(c.buf[p]) + off);
+  float4 acc = v[0];
+#pragma unroll
+  for (int p = 1; p < B200_COMM_MAX_RANKS; ++p)
+    if (p < c.world) {
+      acc.x += v[p].x;
+      acc.y += v[p].y;
+      acc.z += v[p].z;
+      acc.w += v[p].w;
+    }
+  acc.x *= scale;
+  acc.y *= scale;
+  acc.z *= scale;
+  acc.w *= scale;
+  cta_barrier_all_ranks(c, &s_epoch);
+  *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.buf[c.rank]) + off) = acc;
+  if (sgd.enabled) {
+    const int64_t gb = offset / 1024 + b;
+    float dec = sgd.wd, tr = 1.0f;
+    bool skip = false;
+    if (sgd.block_tensor) {
+      const int t = sgd.block_tensor[gb];
+      if (t < 0) {
+        skip = true;
+      } else {
+        dec = sgd.wd * sgd.tdecay[t];
+        if (sgd.trust && sgd.tlars[t] != 0.0f) tr = sgd.trust[t];
+      }
+    }
+    if (!skip) {
+      const int64_t i = gb * 1024 + tid * 4;
+      float4 wv = *reinterpret_cast<const float4*>(sgd.master + i);
+      float4 mv = *reinterpret_cast<const float4*>(sgd.mom + i);
+      float ww[4] = {wv.x, wv.y, wv.z, wv.w}, mm[4] = {mv.x, mv.y, mv.z, mv.w}, gg[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float ge = (gg[k] + dec * ww[k]) * tr;
+        mm[k] = sgd.mu * mm[k] + ge;
+        ww[k] -= sgd.lr * mm[k];
+      }
+      *reinterpret_cast<float4*>(sgd.master + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+      *reinterpret_cast<float4*>(sgd.mom + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+      if (sgd.shadow) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(sgd.shadow + i) = pk;
+      }
+    }
+  }
+  if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
+}
+
 // bf16 payload: 2048 elements per block (256 threads x 8), fp32 accumulation, one rounding.
 __global__ void __launch_bounds__(kThreads) allreduce_bf16_kernel(CommDev c, int64_t offset, int64_t nblk, float scale) {
   __shared__ uint32_t s_epoch;
@@ -297,6 +366,12 @@ int b200_allreduce_f32(const b200_comm* comm, int64_t offset, int64_t n, float s
                sgd->lr, sgd->mu, sgd->wd, 1};
   }
   const int64_t nblk = n / 1024;
+  const int64_t one_shot_max = comm->one_shot_max_bytes > 0 ? comm->one_shot_max_bytes : 0;
+  if (n * 4 <= one_shot_max && nblk <= B200_COMM_MAX_CTAS) {
+    allreduce_f32_oneshot_kernel<<<(int)nblk, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   if (nblk < ctas) ctas = (int)nblk;
   allreduce_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
   B200_LAUNCH_CHECK();

@@ -149,6 +149,19 @@ def launch(num_nodes: int, workers_per_socket: int, batch_size: int, fabric: str
     total = num_nodes * wpn
     for line in layout.banner():
         print(line, file=out)
+    topo = None
+    if device == "gpu":
+        # fabric health probe (the reference runs `ibv_devinfo | grep state` on every node: prep-cluster.sh:23)
+        try:
+            from . import topology
+            topo = topology.discover()
+            for line in topo.report():
+                print(line, file=out)
+            if fabric in ("nvl", "ib") and len(topo.gpus) > 1 and not topo.all_to_all_p2p:
+                print("fabric nvl needs all-to-all peer access; falling back to nccl", file=out)
+                fabric = "nccl"
+        except Exception as e:   # discovery is advisory
+            print(f"topology discovery skipped: {e}", file=out)
     master_port = master_port or int(os.environ.get("MASTER_PORT", 0)) or free_port()
     args = benchmark_args(batch_size, model, num_batches, num_warmup, layout, fabric, device, extra)
     cmd = [sys.executable, "-m", module] + args
@@ -166,6 +179,8 @@ def launch(num_nodes: int, workers_per_socket: int, batch_size: int, fabric: str
                    OMP_NUM_THREADS=str(max(1, layout.intra_threads)),
                    HOROVOD_FUSION_THRESHOLD=os.environ.get("HOROVOD_FUSION_THRESHOLD", str(FUSION_THRESHOLD)))
         sock = min(lr // per_socket, cpu["sockets"] - 1) if workers_per_socket else 0
+        if topo is not None and lr < len(topo.gpus) and 0 <= topo.numa_of(lr) < cpu["sockets"]:
+            sock = topo.numa_of(lr)      # pin the worker next to the NUMA node its GPU hangs off
         cpus = socket_cpus(sock, cpu["sockets"]) if workers_per_socket else sorted(os.sched_getaffinity(0))
         # the pe=<cores> part of --map-by: give each worker its own slice of the socket's cores
         k = lr % per_socket

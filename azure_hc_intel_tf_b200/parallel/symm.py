@@ -114,6 +114,8 @@ class SymmetricContext:
         self.lib = _native.cuda()
         _declare(self.lib)
         self.ctas = int(os.environ.get("B200_COMM_CTAS", "48"))
+        # messages up to this many bytes use the one-shot kernel (one NVLink traversal); 0 disables it
+        self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(128 << 10)))
         self.buffers: List[SymmBuffer] = []
         self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
         self._scratch: Optional[SymmBuffer] = None
@@ -146,7 +148,7 @@ class SymmetricContext:
         for r in range(self.world):
             cs.buf[r] = buf.peers[r]
             cs.pad[r] = self.pad.peers[r]
-        cs.rank, cs.world, cs.ctas, cs.one_shot_max_bytes = self.rank, self.world, self.ctas, 0
+        cs.rank, cs.world, cs.ctas, cs.one_shot_max_bytes = self.rank, self.world, self.ctas, self.one_shot_max_bytes
         return cs
 
     @staticmethod
