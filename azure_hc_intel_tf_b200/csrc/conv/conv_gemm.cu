@@ -11,10 +11,11 @@
 //           read as an MN-major operand with the taps flipped - no transposed weight copy is made
 //   gemm  : A[M,K] row-major, B[N,K] row-major (both TMA tiled)
 //
-// CTA layout (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
-// warps 2..5 = epilogue (TMEM -> registers -> bf16/fp32 -> global). Pipelines: smem ring (full/empty mbarriers)
-// between TMA and MMA; two TMEM accumulator stages (tmem_full/tmem_empty) between MMA and epilogue, so the
-// epilogue of tile i overlaps the main loop of tile i+1.
+// CTA layout (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..5 and 6..9 = two epilogue groups (TMEM -> registers -> bf16 -> swizzled smem -> TMA bulk store, or a
+// cooperative scatter for strided dgrad). Pipelines: smem ring (full/empty mbarriers) between TMA and MMA; two TMEM
+// accumulator stages (tmem_full/tmem_empty), one owned by each epilogue group, so the epilogues of tiles i and i+1
+// overlap each other and the main loop of tile i+2.
 #include "b200conv.h"
 #include "common.cuh"
 #include "conv/tensormap.h"
@@ -28,7 +29,7 @@ using namespace umma;
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;                    // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kMaxBlockN = 256;
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;                  // warp 0 TMA, warp 1 MMA, warps 2-5 and 6-9: two epilogue groups
 constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kAccStages = 2;
 constexpr int kTmemCols = 512;
@@ -202,59 +203,75 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else {
-    // ================================================================ epilogue (warps 2..5)
+    // ================================================================ epilogue (warps 2..5 = group 0, 6..9 = group 1)
     const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
-    int acc = 0;
+    const int grp = (warp - 2) >> 2;            // group g owns TMEM accumulator stage g and tiles g, g+2, ... of this CTA
+    const int acc = grp;
     uint32_t acc_phase = 0;
+    const int eg = threadIdx.x - 64 - grp * 128;    // 0..127 within the group
+    if (p.col_stats) {
+      // running statistics of this (CTA, group): four 32-row-group rows of [2][N] floats, zeroed here (no memset launch)
+      float4* z = reinterpret_cast<float4*>(p.col_stats + ((size_t)blockIdx.x * 2 + grp) * 4 * 2 * p.N);
+      const int n4 = 4 * 2 * p.N / 4;
+      for (int i = eg; i < n4; i += 128) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      __threadfence_block();
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+    }
     if (p.tma_store) {
-      // ---- staged path: TMEM -> registers -> bf16 -> swizzled shared memory -> TMA bulk store; BatchNorm
-      //      statistics are taken from the staged (stored) values with conflict-free shared-memory reads.
-      const int et = threadIdx.x - 64;          // 0..127 within the epilogue group
+      // ---- staged path: TMEM -> registers -> bf16 -> swizzled shared memory -> TMA bulk store (or cooperative
+      //      scatter); BatchNorm statistics are taken from the staged (stored) values with conflict-free reads.
+      const int et = threadIdx.x - 64 - grp * 128;   // 0..127 within the group
       const int r_in_tile = lane_group * 32 + lane;
       const int cp = et & 31;                   // column pair handled for statistics
       const int qtr = et >> 5;                  // 32-row group handled for statistics
-      uint32_t box_counter = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      uint8_t* const buf = out_stage + grp * kStageOutBytes;   // one staging box per group
+      const int bar_id = 1 + grp;
+      bool store_pending = false;
+      int tile_i = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_i) {
+        if ((tile_i & 1) != grp) continue;
         const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
         const int n0 = nt * p.block_n;
-        mbar_wait(&bars->tmem_full[acc], acc_phase);
+        mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
         const int nboxes = p.block_n / 64;
-        for (int bx = 0; bx < nboxes; ++bx, ++box_counter) {
-          uint8_t* buf = out_stage + (box_counter & 1) * kStageOutBytes;
-          // this CTA's running column statistics for (row group qtr, column pair cp) of this box: fetched now, the
-          // latency hides behind the TMEM loads below; only this thread ever touches these addresses
+        for (int bx = 0; bx < nboxes; ++bx) {
+          // this CTA-group's running column statistics for (row group qtr, column pair cp) of this box: fetched now,
+          // the latency hides behind the TMEM loads below; only this thread ever touches these addresses
           float* const st_dst = (p.col_stats && n0 + bx * 64 + cp * 2 < p.N)
-                                    ? p.col_stats + ((size_t)blockIdx.x * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
+                                    ? p.col_stats + (((size_t)blockIdx.x * 2 + grp) * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
                                     : nullptr;
           float2 old1 = make_float2(0.f, 0.f), old2 = make_float2(0.f, 0.f);
           if (st_dst) {
             old1 = __ldcg(reinterpret_cast<const float2*>(st_dst));
             old2 = __ldcg(reinterpret_cast<const float2*>(st_dst + p.N));
           }
-          // the bulk store that read this buffer two boxes ago must have finished reading it
-          if (et == 0 && box_counter >= kOutBufs) tma_store_wait_read<kOutBufs - 1>();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          uint32_t r[32];
+          // TMEM -> registers -> packed bf16 first; only then wait for the staging buffer, so the previous bulk
+          // store's read of the buffer overlaps these loads
+          uint4 pk[8];
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
             tmem_ld_x32(t_row + (uint32_t)(bx * 64 + half * 32), r);
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {       // four 16-byte chunks of 8 bf16
-              uint4 v;
               __nv_bfloat162 t;
 #define PK2(a, b) (t = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b)), *reinterpret_cast<uint32_t*>(&t))
-              v.x = PK2(r[8 * j + 0], r[8 * j + 1]);
-              v.y = PK2(r[8 * j + 2], r[8 * j + 3]);
-              v.z = PK2(r[8 * j + 4], r[8 * j + 5]);
-              v.w = PK2(r[8 * j + 6], r[8 * j + 7]);
+              pk[half * 4 + j].x = PK2(r[8 * j + 0], r[8 * j + 1]);
+              pk[half * 4 + j].y = PK2(r[8 * j + 2], r[8 * j + 3]);
+              pk[half * 4 + j].z = PK2(r[8 * j + 4], r[8 * j + 5]);
+              pk[half * 4 + j].w = PK2(r[8 * j + 6], r[8 * j + 7]);
 #undef PK2
-              const int chunk = half * 4 + j;
-              *reinterpret_cast<uint4*>(buf + r_in_tile * 128 + ((chunk ^ (r_in_tile & 7)) << 4)) = v;
             }
           }
+          // the bulk store that last read this buffer must have finished reading it
+          if (et == 0 && store_pending) tma_store_wait_read<0>();
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+#pragma unroll
+          for (int chunk = 0; chunk < 8; ++chunk)
+            *reinterpret_cast<uint4*>(buf + r_in_tile * 128 + ((chunk ^ (r_in_tile & 7)) << 4)) = pk[chunk];
           if (bx == nboxes - 1) {
             // all of this tile's accumulators are out of TMEM: hand the stage back to the MMA warp
             tc_fence_before();
@@ -262,10 +279,36 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
           }
           fence_proxy_async();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (et == 0) {
-            tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
-            tma_store_commit();
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+          if (!p.scatter) {
+            if (et == 0) {
+              tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
+              tma_store_commit();
+              store_pending = true;
+            }
+          } else {
+            // strided 1x1 dgrad: GEMM row (n,p,q) -> pixel (n, p*sy, q*sx); the skipped pixels get zeros. Eight
+            // threads write one 128-byte row segment, so every store instruction covers whole cache lines.
+            const int chunk = et & 7;
+            const int col = n0 + bx * 64 + chunk * 8;
+            if (col < p.N) {
+#pragma unroll 2
+              for (int pass = 0; pass < 8; ++pass) {
+                const int rr = pass * 16 + (et >> 3);
+                const int row = mt * kBlockM + rr;
+                if (row >= p.M) break;
+                const int img = row / p.PQ;
+                const int rem = row - img * p.PQ;
+                const int pp = rem / p.Q, qq = rem - pp * p.Q;
+                const size_t opix = ((size_t)img * p.H + (size_t)pp * p.sy) * p.W + (size_t)qq * p.sx;
+                const uint4 v = *reinterpret_cast<const uint4*>(buf + rr * 128 + ((chunk ^ (rr & 7)) << 4));
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + opix * p.ldo + col;
+                const uint4 z = make_uint4(0, 0, 0, 0);
+                for (int dy = 0; dy < p.sy; ++dy)
+                  for (int dx = 0; dx < p.sx; ++dx)
+                    *reinterpret_cast<uint4*>(o + ((size_t)dy * p.W + dx) * p.ldo) = (dy | dx) ? z : v;
+              }
+            }
           }
           if (st_dst) {
             float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
@@ -284,18 +327,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             __stcg(reinterpret_cast<float2*>(st_dst + p.N), make_float2(old2.x + s2a, old2.y + s2b));
           }
         }
-        if (++acc == kAccStages) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
+        acc_phase ^= 1;
       }
-      if (et == 0) tma_store_wait<0>();
+      if (et == 0 && store_pending) tma_store_wait<0>();
     } else {
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int tile_i = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_i) {
+        if ((tile_i & 1) != grp) continue;
         const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
         const int row = mt * kBlockM + lane_group * 32 + lane;
         const int n0 = nt * p.block_n;
-        mbar_wait(&bars->tmem_full[acc], acc_phase);
+        mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
         const bool valid = row < p.M;
@@ -340,7 +382,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
             if (lane < 16) {
               const int col = lane;
-              float* dst = p.col_stats + ((size_t)blockIdx.x * 4 + lane_group) * 2 * p.N + n0 + c + col;
+              float* dst = p.col_stats + (((size_t)blockIdx.x * 2 + grp) * 4 + lane_group) * 2 * p.N + n0 + c + col;
               dst[0] += s1[0];
               dst[p.N] += s2[0];
             }
@@ -379,10 +421,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
-        if (++acc == kAccStages) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
+        acc_phase ^= 1;
+      }
+    }
+    if (p.col_stats) {
+      // fold this CTA's 8 running rows (2 groups x 4 row groups) into one row of the compact result region that
+      // follows the scratch rows, in a fixed order; bn_finalize_partials then reads one row per CTA
+      __threadfence_block();
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+      const int e8 = threadIdx.x - 64;          // 0..255
+      const float* src = p.col_stats + (size_t)blockIdx.x * 8 * 2 * p.N;
+      float* dst = p.col_stats + (size_t)gridDim.x * 8 * 2 * p.N + (size_t)blockIdx.x * 2 * p.N;
+      for (int i = e8; i < 2 * p.N; i += 256) {
+        float a = 0.0f;
+#pragma unroll
+        for (int rrow = 0; rrow < 8; ++rrow) a += __ldcg(src + (size_t)rrow * 2 * p.N + i);
+        dst[i] = a;
       }
     }
   }
@@ -416,8 +470,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   const int stage_bytes = kABytes + p.block_n * kBlockK * 2;
   // bf16 row-major outputs whose tile width is a multiple of 64 go out through shared memory + TMA bulk stores
   CUtensorMap mo;
-  p.tma_store = (!p.out_fp32 && !p.scatter && p.block_n % 64 == 0 && p.N % 8 == 0 && p.ldo % 8 == 0) ? 1 : 0;
-  if (p.tma_store) {
+  p.tma_store = (!p.out_fp32 && p.block_n % 64 == 0 && p.N % 8 == 0 && p.ldo % 8 == 0) ? 1 : 0;
+  if (p.tma_store && !p.scatter) {
     if (tmap_tiled_2d(&mo, p.out, 2, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldo * 2, 64, kBlockM, true)) return -1;
   } else {
     mo = ma;   // unused
@@ -499,19 +553,24 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   p.out = y;
   p.ldo = g->k;
   p.col_stats = col_stats;
-  if (col_stats)   // per-CTA running sums start at zero
-    B200_CUDA(cudaMemsetAsync(col_stats, 0, sizeof(float) * 2 * (size_t)g->k * (size_t)b200_conv_stats_rows(g),
-                              static_cast<cudaStream_t>(stream)));
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 
+static int64_t grid_for_tiles(int64_t m, int n) {
+  const int bn = pick_block_n(n);
+  int64_t tiles = (m + kBlockM - 1) / kBlockM * ((n + bn - 1) / bn);
+  return tiles < kNumSMs ? tiles : kNumSMs;
+}
+
 int64_t b200_conv_stats_rows(const b200_conv_geom* g) {
-  // one row per (CTA, 32-row group): the persistent grid has at most one CTA per SM
+  // per CTA of the persistent grid: 8 scratch rows (epilogue group x 32-row group) + 1 folded row at the end
   if (!g) return -1;
-  const int64_t m = (int64_t)g->n * g->p * g->q;
-  const int bn = pick_block_n(g->k);
-  int64_t tiles = (m + kBlockM - 1) / kBlockM * ((g->k + bn - 1) / bn);
-  return (tiles < kNumSMs ? tiles : kNumSMs) * 4;
+  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 9;
+}
+
+int64_t b200_conv_stats_first_result_row(const b200_conv_geom* g) {
+  if (!g) return -1;
+  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 8;
 }
 
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream) {
@@ -596,11 +655,8 @@ int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, i
   return b200_gemm_nt_stats(a, b, out, m, n, k, ldo, out_fp32, nullptr, stream);
 }
 
-int64_t b200_gemm_stats_rows(int32_t m, int32_t n) {
-  const int bn = pick_block_n(n);
-  int64_t tiles = ((int64_t)m + kBlockM - 1) / kBlockM * ((n + bn - 1) / bn);
-  return (tiles < kNumSMs ? tiles : kNumSMs) * 4;
-}
+int64_t b200_gemm_stats_rows(int32_t m, int32_t n) { return grid_for_tiles(m, n) * 9; }
+int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n) { return grid_for_tiles(m, n) * 8; }
 
 int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
                        int32_t ldo, int32_t out_fp32, float* col_stats, void* stream) {
@@ -622,9 +678,6 @@ int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_
   p.ldo = ldo;
   p.out_fp32 = out_fp32;
   p.col_stats = col_stats;
-  if (col_stats)
-    B200_CUDA(cudaMemsetAsync(col_stats, 0, sizeof(float) * 2 * (size_t)n * (size_t)b200_gemm_stats_rows(m, n),
-                              static_cast<cudaStream_t>(stream)));
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 

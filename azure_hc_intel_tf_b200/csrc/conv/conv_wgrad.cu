@@ -169,7 +169,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     }
   } else {
     const int lane_group = warp & 3;
-    mbar_wait(&bars->tmem_full, 0);
+    mbar_wait_backoff(&bars->tmem_full, 0);
     tc_fence_after();
     const size_t ld = (size_t)p.rows_total;       // dw[k][rows_total]
     float* const outp = p.ws ? p.ws + (size_t)slice * p.out_elems : p.dw;

@@ -62,6 +62,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// For long waits by many warps (epilogue warps waiting for a whole main loop): back off between probes so the
+// waiting warps do not take issue slots from the TMA-producer and MMA-issuer warps.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(200);
+}
+
 // ---------------------------------------------------------------------------------------- TMA
 
 __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* m) {

@@ -57,7 +57,9 @@ def fprop(x, w_lp, m, want_stats: bool = False):
         rows = lib().b200_conv_stats_rows(C.byref(g))
         stats = torch.empty((rows, 2, g.k), dtype=torch.float32, device=x.device)
     _check(lib().b200_conv_fprop(_ptr(x), _ptr(w_lp), _ptr(y), C.byref(g), _ptr(stats), _stream()), "conv_fprop")
-    return (y, stats) if want_stats else y
+    if want_stats:   # the leading rows are kernel scratch; results are one row per CTA after them
+        return y, stats[lib().b200_conv_stats_first_result_row(C.byref(g)):]
+    return y
 
 
 def stats_reduce(stats):
@@ -156,6 +158,8 @@ def first_layer_fprop(x, w_lp, m, want_stats: bool):
         stats = torch.empty((srows, 2, g.k), dtype=torch.float32, device=x.device)
     _check(lib().b200_gemm_nt_stats(_ptr(a), _ptr(w2), _ptr(y), rows, g.k, kpad, g.k, 0, _ptr(stats), _stream()),
            "gemm_nt_stats")
+    if stats is not None:
+        stats = stats[lib().b200_gemm_stats_first_result_row(rows, g.k):]
     return y, stats, a
 
 

@@ -31,12 +31,15 @@ enum { B200_CONV_FPROP = 0, B200_CONV_DGRAD = 1, B200_CONV_WGRAD = 2 };
 int b200_conv_supported(const b200_conv_geom* g, int op);
 
 /* y[n,p,q,k] = sum_{r,s,c} x[n, p*sh - pad_t + r, q*sw - pad_l + s, c] * w[k,r,s,c].
- * col_stats (optional): [b200_conv_stats_rows(g)][2][k] fp32 partial column sums and sums of squares of the
- * stored (bf16-rounded) outputs, one row per (CTA, 32-row group) — the batch-norm statistics, produced by the
- * epilogue so that y is not read again. The buffer is zeroed by the call; fold it with b200_bn_finalize_partials. */
+ * col_stats (optional): [b200_conv_stats_rows(g)][2][k] fp32 buffer for the batch-norm statistics of the stored
+ * (bf16-rounded) outputs, produced by the epilogue so that y is not read again. The first
+ * b200_conv_stats_first_result_row(g) rows are kernel scratch; the rows from there on (one per CTA of the persistent
+ * grid) hold partial column sums [0][k] and sums of squares [1][k] — fold those with b200_bn_finalize_partials.
+ * The kernel initialises everything it reads; no memset is needed. */
 int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
                     void* stream);
 int64_t b200_conv_stats_rows(const b200_conv_geom* g);
+int64_t b200_conv_stats_first_result_row(const b200_conv_geom* g);
 
 /* dx = gradient of fprop wrt x. Stride 1 (any filter), or strided 1x1 without padding. */
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);
@@ -53,10 +56,11 @@ int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, i
                  int32_t out_fp32, void* stream);
 
 /* b200_gemm_nt that also emits per-column statistics of the stored outputs, like b200_conv_fprop
- * (col_stats: [b200_gemm_stats_rows(m, n)][2][n] fp32, zeroed by the call). */
+ * (col_stats: [b200_gemm_stats_rows(m, n)][2][n] fp32; results start at row b200_gemm_stats_first_result_row). */
 int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
                        int32_t ldo, int32_t out_fp32, float* col_stats, void* stream);
 int64_t b200_gemm_stats_rows(int32_t m, int32_t n);
+int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n);
 
 /* Patch matrix for small-Cin (first-layer) convolutions: a[n*p*q][kpad] bf16, column (r*S + s)*Cin + c, zero padded
  * from R*S*Cin up to kpad (a multiple of 64). Forward: gemm_nt(a, w_padded); weight gradient: dense_wgrad(a, dy). */
