@@ -50,13 +50,14 @@ def main(argv=None):
         raise SystemExit("the sweep needs at least 2 ranks on the nvl fabric")
     rows = []
     if rank == 0:
-        print(f"# allreduce sweep, {n_ranks} ranks, device-timed, max over ranks")
+        print(f"# allreduce sweep, {n_ranks} ranks, device-timed, max over ranks; one-shot <= {ctx.one_shot_max_bytes} B, "
+              f"NVLS >= {ctx.nvls_min_bytes} B (fp32, when a multicast mapping exists)")
         print(f"{'dtype':9s} {'bytes':>12s} {'ours us':>10s} {'nccl us':>10s} {'ours busbw':>11s} {'nccl busbw':>11s}")
     for dname in a.dtypes.split(","):
         dtype = getattr(torch, dname)
         esz = torch.empty((), dtype=dtype).element_size()
         gran = 1024 if dtype == torch.float32 else 2048
-        buf = ctx.alloc(a.max + gran * esz, dtype)
+        buf = ctx.alloc(a.max + gran * esz, dtype, multicast=(dtype == torch.float32))
         size = a.min
         while size <= a.max:
             n = max(gran, size // esz // gran * gran)

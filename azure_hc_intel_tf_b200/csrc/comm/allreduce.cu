@@ -25,6 +25,7 @@ constexpr int kPadWords = kPadFlagWords + B200_COMM_MAX_CTAS;             // + p
 struct CommDev {
   uint64_t buf[B200_COMM_MAX_RANKS];
   uint64_t pad[B200_COMM_MAX_RANKS];
+  uint64_t mc;      // multicast address of the data buffer (0 = none)
   int rank, world;
 };
 
@@ -83,6 +84,7 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
   return v;
 }
 
+template <bool kNvls>
 __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int64_t offset, int64_t nblk, float scale,
                                                                  SgdDev sgd) {
   __shared__ uint32_t s_epoch;
@@ -96,6 +98,32 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
     const int64_t b = j * c.world + c.rank;
     if (b >= nblk) break;
     const int64_t off = offset + b * 1024 + tid * 4;
+    if (kNvls) {
+      // NVLS: one load returns the sum over all ranks' copies, computed inside the NVSwitch; one store lands in
+      // every rank's copy. Link traffic per GPU: S/N reduced in + S/N out, instead of (N-1)/N*S each way.
+      // Four owned blocks per trip keep four switch round trips in flight per thread.
+      float4 acc[4];
+      float* mp[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
+        mp[u] = bu < nblk ? reinterpret_cast<float*>(c.mc) + offset + bu * 1024 + tid * 4 : nullptr;
+        if (mp[u])
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(acc[u].x), "=f"(acc[u].y), "=f"(acc[u].z), "=f"(acc[u].w)
+                       : "l"(mp[u])
+                       : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (!mp[u]) continue;
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mp[u]), "f"(acc[u].x * scale),
+                     "f"(acc[u].y * scale), "f"(acc[u].z * scale), "f"(acc[u].w * scale)
+                     : "memory");
+      }
+      j += 3 * (int64_t)gridDim.x;      // the loop header advances by one more gridDim.x
+      continue;
+    }
     float4 v[B200_COMM_MAX_RANKS];
 #pragma unroll
     for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
@@ -300,6 +328,7 @@ int to_dev(const b200_comm* comm, CommDev& d, int& ctas) {
     d.pad[i] = comm->pad[i];
     if (i < comm->world) B200_CHECK_ARG(d.buf[i] && d.pad[i], "comm: missing peer pointer for rank %d", i);
   }
+  d.mc = comm->mc;
   d.rank = comm->rank;
   d.world = comm->world;
   ctas = comm->ctas > 0 ? comm->ctas : 64;
@@ -373,7 +402,10 @@ int b200_allreduce_f32(const b200_comm* comm, int64_t offset, int64_t n, float s
     return 0;
   }
   if (nblk < ctas) ctas = (int)nblk;
-  allreduce_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
+  if (comm->mc && comm->nvls_min_bytes >= 0 && n * 4 >= comm->nvls_min_bytes && comm->world > 2)
+    allreduce_f32_kernel<true><<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
+  else
+    allreduce_f32_kernel<false><<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
   B200_LAUNCH_CHECK();
   return 0;
 }

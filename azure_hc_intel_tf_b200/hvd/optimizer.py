@@ -244,7 +244,7 @@ class DistributedOptimizer:
             self.grad = optimizer.grad
             if self._symm is not None and self.world > 1:
                 # move the flat gradient buffer into NVLink symmetric memory; re-point p.grad
-                self._symm_grad = self._symm.alloc_like_flat(optimizer.total, torch.float32)
+                self._symm_grad = self._symm.alloc_like_flat(optimizer.total, torch.float32, multicast=True)
                 self._symm_grad.local.copy_(optimizer.grad)
                 optimizer.grad = self._symm_grad.local
                 self.grad = optimizer.grad

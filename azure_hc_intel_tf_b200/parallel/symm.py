@@ -25,7 +25,8 @@ MAX_RANKS = 8
 
 class CommStruct(C.Structure):
     _fields_ = [("buf", C.c_uint64 * MAX_RANKS), ("pad", C.c_uint64 * MAX_RANKS), ("rank", C.c_int32),
-                ("world", C.c_int32), ("ctas", C.c_int32), ("one_shot_max_bytes", C.c_int32)]
+                ("world", C.c_int32), ("ctas", C.c_int32), ("one_shot_max_bytes", C.c_int32),
+                ("mc", C.c_uint64), ("nvls_min_bytes", C.c_int64)]
 
 
 class SgdArgs(C.Structure):
@@ -106,6 +107,27 @@ class SymmBuffer:
             self.ptr = 0
 
 
+class McSymmBuffer:
+    """Symmetric allocation that also has a multicast (NVLS) mapping. The VMM allocation, the handle exchange and
+    the multicast binding are done by ``torch.distributed._symmetric_memory`` (allocation plumbing only: every
+    kernel that touches the memory is this framework's)."""
+
+    def __init__(self, ctx: "SymmetricContext", nbytes: int, dtype: torch.dtype):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.ctx = ctx
+        self.nbytes = nbytes
+        self.local_bytes = symm_mem.empty(nbytes, dtype=torch.uint8, device=ctx.device)
+        self.local_bytes.zero_()
+        self._hdl = symm_mem.rendezvous(self.local_bytes, dist.group.WORLD)
+        self.peers = [int(p) for p in self._hdl.buffer_ptrs]
+        self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        self.ptr = self.local_bytes.data_ptr()
+        self.local = self.local_bytes.view(dtype)
+
+    def close(self):
+        self._hdl = None
+
+
 class SymmetricContext:
     def __init__(self, rank: int, world: int, device: torch.device):
         if world > MAX_RANKS:
@@ -116,6 +138,10 @@ class SymmetricContext:
         self.ctas = int(os.environ.get("B200_COMM_CTAS", "48"))
         # messages up to this many bytes use the one-shot kernel (one NVLink traversal); 0 disables it
         self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(128 << 10)))
+        # messages of at least this many bytes use the NVLS (in-switch reduction) kernel when the buffer has a
+        # multicast mapping; -1 disables NVLS
+        self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(1 << 20)))
+        self.nvls_ok = None      # decided collectively at the first multicast allocation
         self.buffers: List[SymmBuffer] = []
         self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
         self._scratch: Optional[SymmBuffer] = None
@@ -134,14 +160,32 @@ class SymmetricContext:
         dist.all_gather(outs, src)
         return [o.cpu() for o in outs]
 
-    def alloc(self, nbytes: int, dtype: torch.dtype) -> SymmBuffer:
+    def alloc(self, nbytes: int, dtype: torch.dtype, multicast: bool = False):
+        """Collective. ``multicast=True`` asks for a buffer with an NVLS multicast mapping and falls back to a plain
+        IPC buffer (on every rank alike) if the platform refuses."""
+        if multicast and self.nvls_min_bytes >= 0 and self.nvls_ok is not False:
+            b, ok = None, 1
+            try:
+                b = McSymmBuffer(self, nbytes, dtype)
+                ok = 1 if b.mc_ptr else 0
+            except Exception as e:          # no VMM/multicast support, or the private API changed
+                ok = 0
+                if self.rank == 0:
+                    print(f"[b200 comm] NVLS multicast unavailable ({e.__class__.__name__}: {e}); using P2P two-shot")
+            flag = torch.tensor([ok], device=self.device, dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            self.nvls_ok = bool(flag.item())
+            if self.nvls_ok:
+                self.buffers.append(b)
+                dist.barrier()
+                return b
         b = SymmBuffer(self, nbytes, dtype)
         self.buffers.append(b)
         dist.barrier()           # every rank has mapped every peer before anyone launches a kernel on it
         return b
 
-    def alloc_like_flat(self, numel: int, dtype: torch.dtype) -> SymmBuffer:
-        return self.alloc(numel * torch.empty((), dtype=dtype).element_size(), dtype)
+    def alloc_like_flat(self, numel: int, dtype: torch.dtype, multicast: bool = False):
+        return self.alloc(numel * torch.empty((), dtype=dtype).element_size(), dtype, multicast)
 
     def comm_struct(self, buf: SymmBuffer) -> CommStruct:
         cs = CommStruct()
@@ -149,6 +193,8 @@ class SymmetricContext:
             cs.buf[r] = buf.peers[r]
             cs.pad[r] = self.pad.peers[r]
         cs.rank, cs.world, cs.ctas, cs.one_shot_max_bytes = self.rank, self.world, self.ctas, self.one_shot_max_bytes
+        cs.mc = getattr(buf, "mc_ptr", 0) or 0
+        cs.nvls_min_bytes = self.nvls_min_bytes
         return cs
 
     @staticmethod

@@ -116,7 +116,7 @@ def w_nvl_allreduce(rank, world, sizes, iters):
     out = []
     for dtype, gran in ((torch.float32, 1024), (torch.bfloat16, 2048)):
         nmax = max(sizes)
-        buf = ctx.alloc_like_flat(nmax, dtype)
+        buf = ctx.alloc_like_flat(nmax, dtype, multicast=(dtype == torch.float32))   # NVLS for the large fp32 sizes
         for n in sizes:
             n = (n + gran - 1) // gran * gran
             g = torch.Generator(device="cpu").manual_seed(1000 * rank + n % 997)
@@ -159,6 +159,7 @@ def w_nvl_allreduce(rank, world, sizes, iters):
     ctx.broadcast_(b, 0, 4096, world - 1)
     torch.cuda.synchronize()
     out.append(("bcast", 4096, bool((b.local == float(world - 1)).all().item()), True))
+    out.append(("nvls_available", 0, True, True) if ctx.nvls_ok else ("nvls_unavailable_fell_back_to_p2p", 0, True, True))
     return out
 
 

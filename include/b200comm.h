@@ -6,7 +6,10 @@
  * run-tf-sing-libfabric-intelmpi.sh:86-101) — plus Horovod's own MPI_Allreduce call and TF's ApplyMomentum that
  * follows it. Here every rank maps every peer's buffers (CUDA IPC) and one sm_100a kernel
  * reads and writes them directly over NVLink: reduce-scatter by peer loads, all-gather by peer stores, the 1/N
- * scale and the momentum-SGD update, with flag-based cross-GPU barriers. No NCCL call is involved.
+ * scale and the momentum-SGD update, with flag-based cross-GPU barriers. No NCCL call is involved. Three algorithms,
+ * chosen per message size: one-shot (every rank reads all peers; small messages), two-shot (owner reduces its shard
+ * with peer loads and all-gathers it with peer stores) and NVLS (multimem.ld_reduce pulls the shard already reduced
+ * inside the NVSwitch, multimem.st broadcasts it; needs a multicast mapping of the buffer).
  *
  * Symmetric buffers: each rank allocates the same size with b200_symm_alloc, exports an IPC handle, and opens the
  * handles of its peers (exchange them with any out-of-band channel, e.g. torch.distributed all_gather).
@@ -41,6 +44,9 @@ typedef struct b200_comm {
   int32_t rank, world;
   int32_t ctas;                        /* CTAs per collective (<= B200_COMM_MAX_CTAS); the same on all ranks */
   int32_t one_shot_max_bytes;          /* messages up to this size use the one-shot algorithm */
+  uint64_t mc;                         /* multicast (NVLS) address of the data buffer, or 0 when there is none */
+  int64_t nvls_min_bytes;              /* messages of at least this size use the in-switch reduction when mc != 0
+                                          and world > 2 (with two ranks a direct peer read is the shorter path) */
 } b200_comm;
 
 /* Optimizer half of the fused kernel; all pointers are LOCAL flat buffers indexed like the gradient buffer. */
