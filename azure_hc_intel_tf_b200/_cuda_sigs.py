@@ -26,9 +26,9 @@ SIGS = {
     "b200_bn_stats": (i32, [vp, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp, vp]),
     "b200_bn_finalize": (i32, [vp, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
     "b200_bn_finalize_partials": (i32, [vp, i64, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
-    "b200_bn_apply": (i32, [vp, vp, vp, i64, i32, vp, vp, i32, vp]),
-    "b200_bn_bwd_reduce": (i32, [vp, vp, vp, i64, i32, vp, vp, vp, vp, i32, vp, vp, vp, vp]),
-    "b200_bn_bwd_apply": (i32, [vp, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, vp, i32, vp]),
+    "b200_bn_apply": (i32, [vp, vp, vp, vp, i64, i32, vp, vp, i32, vp]),
+    "b200_bn_bwd_reduce": (i32, [vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, i32, vp, vp, vp, vp]),
+    "b200_bn_bwd_apply": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, vp, i32, vp]),
     "b200_bias_act": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "b200_bias_act_bwd": (i32, [vp, vp, vp, vp, i64, i32, i32, vp, vp]),
     "b200_maxpool_fwd": (i32, [vp, vp, vp, C.POINTER(PoolGeom), vp]),

@@ -83,6 +83,7 @@ struct StatsPolicy {
 
 struct BwdReducePolicy {
   const b200_bf16 *dz, *x, *z;
+  const uint8_t* mask;     // optional: one byte per 8-channel vector, bit k = (output k of the forward ReLU was > 0)
   const float *mean, *rstd, *scale, *shift;
   int relu;
   float *dgamma, *dbeta;
@@ -91,7 +92,7 @@ struct BwdReducePolicy {
 
   __device__ __forceinline__ void prepare(int cv) {
     const int ch = cv * 8;
-    if (relu && !z) {
+    if (relu && !z && !mask) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         k_scale[i] = scale[ch + i];
@@ -104,7 +105,13 @@ struct BwdReducePolicy {
     float g[8], xv[8];
     const int64_t off = row * c + cv * 8;
     const bf16x8 gq = ld8_stream(dz + off), xq = ld8_stream(x + off);
-    if (relu && z) {
+    if (relu && mask) {
+      const unsigned mb = __ldg(mask + (off >> 3));
+      unpack8(gq, g);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g[i] = (mb >> i) & 1u ? g[i] : 0.0f;
+      unpack8(xq, xv);
+    } else if (relu && z) {
       float zv[8];
       unpack8(ld8_stream(z + off), zv);
       unpack8(gq, g);
@@ -292,7 +299,8 @@ __device__ __forceinline__ void load8f(const float* p, float o[8]) {
 }
 
 __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restrict__ x, const b200_bf16* __restrict__ res,
-                                                       b200_bf16* __restrict__ z, int64_t nvec, int cvecs,
+                                                       b200_bf16* __restrict__ z, uint8_t* __restrict__ mask_out,
+                                                       int64_t nvec, int cvecs,
                                                        const float* __restrict__ scale, const float* __restrict__ shift,
                                                        int relu, int fixed) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -331,6 +339,12 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restri
         for (int k = 0; k < 8; ++k) f[k] += r[k];
       }
       if (relu) {
+        if (mask_out) {
+          unsigned mb = 0;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) mb |= (f[k] > 0.0f ? 1u : 0u) << k;
+          mask_out[idx] = (uint8_t)mb;
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.0f);
       }
@@ -341,7 +355,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restri
 
 // dx = A*g + B*x + C with g = dz masked by the ReLU; A = scale, B = -scale*dgamma*rstd/M, C = -scale*dbeta/M - B*mean
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const b200_bf16* __restrict__ dz, const b200_bf16* __restrict__ x,
-                                                           const b200_bf16* __restrict__ z, b200_bf16* __restrict__ dx,
+                                                           const b200_bf16* __restrict__ z, const uint8_t* __restrict__ mask,
+                                                           b200_bf16* __restrict__ dx,
                                                            b200_bf16* __restrict__ dres, int64_t nvec, int cvecs,
                                                            float inv_rows, const float* __restrict__ mean,
                                                            const float* __restrict__ rstd, const float* __restrict__ scale,
@@ -372,7 +387,11 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const b200_bf16* __re
       g1 = ld8_stream(dz + (i + stride) * 8);
       x1 = ld8_stream(x + (i + stride) * 8);
     }
-    if (relu && z) {
+    unsigned m0 = 0, m1 = 0;
+    if (relu && mask) {
+      m0 = __ldg(mask + i);
+      if (two) m1 = __ldg(mask + i + stride);
+    } else if (relu && z) {
       z0 = ld8_stream(z + i * 8);
       if (two) z1 = ld8_stream(z + (i + stride) * 8);
     }
@@ -385,7 +404,11 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const b200_bf16* __re
       unpack8(k2 ? g1 : g0, g);
       unpack8(k2 ? x1 : x0, xv);
       if (relu) {
-        if (z) {
+        if (mask) {
+          const unsigned mb = k2 ? m1 : m0;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) g[k] = (mb >> k) & 1u ? g[k] : 0.0f;
+        } else if (z) {
           float zv[8];
           unpack8(k2 ? z1 : z0, zv);
 #pragma unroll
@@ -526,36 +549,36 @@ int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows
   return 0;
 }
 
-int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, int64_t rows, int32_t c,
-                  const float* scale, const float* shift, int32_t relu, void* stream) {
+int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, uint8_t* relu_mask, int64_t rows,
+                  int32_t c, const float* scale, const float* shift, int32_t relu, void* stream) {
   B200_CHECK_ARG(x && z && scale && shift, "bn_apply: null pointer");
   B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_apply: need c%%8==0 (c=%d)", c);
   int64_t nvec = rows * (c / 8);
   ElemGrid e = elem_grid(nvec, c / 8);
-  bn_apply_kernel<<<e.blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, residual, z, nvec, c / 8, scale, shift,
-                                                                          relu, e.fixed);
+  bn_apply_kernel<<<e.blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, residual, z, relu_mask, nvec, c / 8, scale,
+                                                                          shift, relu, e.fixed);
   B200_LAUNCH_CHECK();
   return 0;
 }
 
-int b200_bn_bwd_reduce(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, int64_t rows, int32_t c,
-                       const float* mean, const float* rstd, const float* scale, const float* shift, int32_t relu,
+int b200_bn_bwd_reduce(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, const uint8_t* relu_mask,
+                       int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale, const float* shift, int32_t relu,
                        float* dgamma, float* dbeta, void* scratch, void* stream) {
   B200_CHECK_ARG(dz && x && mean && rstd && scale && shift && dgamma && dbeta && scratch, "bn_bwd_reduce: null pointer");
   B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_bwd_reduce: need c%%8==0 (c=%d)", c);
-  BwdReducePolicy pol{dz, x, z, mean, rstd, scale, shift, relu, dgamma, dbeta, c};
+  BwdReducePolicy pol{dz, x, z, relu_mask, mean, rstd, scale, shift, relu, dgamma, dbeta, c};
   return launch_col_reduce(pol, rows, c, scratch, static_cast<cudaStream_t>(stream));
 }
 
-int b200_bn_bwd_apply(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, b200_bf16* dx, b200_bf16* dres,
-                      int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale,
+int b200_bn_bwd_apply(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, const uint8_t* relu_mask,
+                      b200_bf16* dx, b200_bf16* dres, int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale,
                       const float* shift, const float* dgamma, const float* dbeta, int32_t relu, void* stream) {
   B200_CHECK_ARG(dz && x && dx && mean && rstd && scale && shift && dgamma && dbeta, "bn_bwd_apply: null pointer");
   B200_CHECK_ARG(rows > 0 && c > 0 && c % 8 == 0, "bn_bwd_apply: need c%%8==0 (c=%d)", c);
   int64_t nvec = rows * (c / 8);
   ElemGrid e = elem_grid(nvec, c / 8);
   bn_bwd_apply_kernel<<<e.blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      dz, x, z, dx, dres, nvec, c / 8, 1.0f / (float)rows, mean, rstd, scale, shift, dgamma, dbeta, relu, e.fixed);
+      dz, x, z, relu_mask, dx, dres, nvec, c / 8, 1.0f / (float)rows, mean, rstd, scale, shift, dgamma, dbeta, relu, e.fixed);
   B200_LAUNCH_CHECK();
   return 0;
 }

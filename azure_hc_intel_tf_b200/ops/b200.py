@@ -96,7 +96,7 @@ def lowp(p: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------ BN pieces
 
-def bn_forward(y, bn, residual, relu, sums=None):
+def bn_forward(y, bn, residual, relu, sums=None, want_mask=False):
     """y: conv output (bf16 NHWC). Returns (z, saved) with saved = (mean, rstd, scale, shift). ``sums``
     ([rows,2,C] fp32 partial Σy, Σy²) comes from the conv epilogue when available, which saves one read of y."""
     n, c, h, w = y.shape
@@ -120,24 +120,26 @@ def bn_forward(y, bn, residual, relu, sums=None):
         scale.copy_(bn.gamma.detach() * rstd)
         shift.copy_(bn.beta.detach() - mean * scale)
     z = empty_nhwc(n, c, h, w, dev)
-    _check(lib().b200_bn_apply(_ptr(y), _ptr(residual), _ptr(z), rows, c, _ptr(scale), _ptr(shift), int(relu),
+    # with a residual the ReLU mask cannot be recomputed from y: keep it as one bit per element for the backward
+    mask = torch.empty(rows * c // 8, dtype=torch.uint8, device=dev) if (relu and residual is not None and want_mask) else None
+    _check(lib().b200_bn_apply(_ptr(y), _ptr(residual), _ptr(z), _ptr(mask), rows, c, _ptr(scale), _ptr(shift), int(relu),
                                _stream()), "bn_apply")
-    return z, stats
+    return (z, stats, mask) if want_mask else (z, stats)
 
 
-def bn_backward(dz, y, z_for_mask, stats, relu, want_dres, dgamma_out, dbeta_out):
+def bn_backward(dz, y, z_for_mask, stats, relu, want_dres, dgamma_out, dbeta_out, mask=None):
     n, c, h, w = y.shape
     rows = n * h * w
     dev = y.device
     mean, rstd, scale, shift = stats[0], stats[1], stats[2], stats[3]
     dgamma = dgamma_out if dgamma_out is not None else torch.empty(c, dtype=torch.float32, device=dev)
     dbeta = dbeta_out if dbeta_out is not None else torch.empty(c, dtype=torch.float32, device=dev)
-    _check(lib().b200_bn_bwd_reduce(_ptr(dz), _ptr(y), _ptr(z_for_mask), rows, c, _ptr(mean), _ptr(rstd), _ptr(scale),
+    _check(lib().b200_bn_bwd_reduce(_ptr(dz), _ptr(y), _ptr(z_for_mask), _ptr(mask), rows, c, _ptr(mean), _ptr(rstd), _ptr(scale),
                                     _ptr(shift), int(relu), _ptr(dgamma), _ptr(dbeta), _ptr(scratch(dev)), _stream()),
            "bn_bwd_reduce")
     dy = empty_nhwc(n, c, h, w, dev)
     dres = empty_nhwc(n, c, h, w, dev) if want_dres else None
-    _check(lib().b200_bn_bwd_apply(_ptr(dz), _ptr(y), _ptr(z_for_mask), _ptr(dy), _ptr(dres), rows, c, _ptr(mean),
+    _check(lib().b200_bn_bwd_apply(_ptr(dz), _ptr(y), _ptr(z_for_mask), _ptr(mask), _ptr(dy), _ptr(dres), rows, c, _ptr(mean),
                                    _ptr(rstd), _ptr(scale), _ptr(shift), _ptr(dgamma), _ptr(dbeta), int(relu),
                                    _stream()), "bn_bwd_apply")
     return dy, dres, dgamma, dbeta
@@ -162,9 +164,9 @@ class _ConvBlock(torch.autograd.Function):
         if m.bn is not None:
             if not first:
                 y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
-            z, stats = bn_forward(y, m.bn, residual, relu, sums)
-            # the ReLU mask is recomputed from y when there is no residual, else read from z
-            ctx.save_for_backward(x, w_lp, y, z if (relu and residual is not None) else None, stats)
+            z, stats, mask = bn_forward(y, m.bn, residual, relu, sums, want_mask=True)
+            # the ReLU mask is recomputed from y when there is no residual, else kept as one bit per element
+            ctx.save_for_backward(x, w_lp, y, mask, stats)
         else:
             if not first:
                 y = conv_impl.fprop(x, w_lp, m)
@@ -187,7 +189,7 @@ class _ConvBlock(torch.autograd.Function):
         if m.bn is not None:
             g_gamma = _direct(gamma) if (gamma is not None and gamma.requires_grad) else None
             g_beta = _direct(beta)
-            dy, dres, dgamma, dbeta = bn_backward(dz, y, z, stats, relu, ctx.has_res, g_gamma, g_beta)
+            dy, dres, dgamma, dbeta = bn_backward(dz, y, None, stats, relu, ctx.has_res, g_gamma, g_beta, mask=z)
         else:
             n, c, h, w = dz.shape
             if bias is not None:

@@ -96,20 +96,22 @@ int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows
                               const float* beta, float* running_mean, float* running_var, float decay, float eps,
                               float* mean, float* rstd, float* scale, float* shift, void* stream);
 
-/* z = act(scale*x + shift (+ residual)); relu != 0 applies max(0, .). residual may be NULL. In place allowed. */
-int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, int64_t rows, int32_t c,
-                  const float* scale, const float* shift, int32_t relu, void* stream);
+/* z = act(scale*x + shift (+ residual)); relu != 0 applies max(0, .). residual may be NULL. In place allowed.
+ * relu_mask (optional, rows*c/8 bytes): bit k of byte v = (element 8v+k passed the ReLU); the backward kernels read
+ * it instead of z, 16x fewer bytes — used when the mask cannot be recomputed from x alone (residual add). */
+int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, uint8_t* relu_mask, int64_t rows,
+                  int32_t c, const float* scale, const float* shift, int32_t relu, void* stream);
 
 /* Backward, pass 1: dbeta[c] = Σ dzm, dgamma[c] = Σ dzm*xhat with dzm = dz masked by the ReLU
- * (mask from z when z != NULL, else recomputed from scale*x+shift; relu == 0 → no mask). Needs the same
- * scratch as b200_bn_stats. */
-int b200_bn_bwd_reduce(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, int64_t rows, int32_t c,
-                       const float* mean, const float* rstd, const float* scale, const float* shift, int32_t relu,
+ * (mask from relu_mask when given, else from z when z != NULL, else recomputed from scale*x+shift; relu == 0 → no
+ * mask). Needs the same scratch as b200_bn_stats. */
+int b200_bn_bwd_reduce(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, const uint8_t* relu_mask,
+                       int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale, const float* shift, int32_t relu,
                        float* dgamma, float* dbeta, void* scratch, void* stream);
 
 /* Backward, pass 2: dx = scale*(dzm - dbeta/rows - xhat*dgamma/rows); dres = dzm when dres != NULL. */
-int b200_bn_bwd_apply(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, b200_bf16* dx, b200_bf16* dres,
-                      int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale,
+int b200_bn_bwd_apply(const b200_bf16* dz, const b200_bf16* x, const b200_bf16* z, const uint8_t* relu_mask,
+                      b200_bf16* dx, b200_bf16* dres, int64_t rows, int32_t c, const float* mean, const float* rstd, const float* scale,
                       const float* shift, const float* dgamma, const float* dbeta, int32_t relu, void* stream);
 
 /* ------------------------------------------------------------------ bias / ReLU (VGG-style conv, affine) */

@@ -70,6 +70,12 @@ def test_bn_forward_backward(n, c, h, w, relu, res):
     assert torch.allclose(dy.float(), yf.grad, atol=3e-2, rtol=5e-2)
     if res:
         assert torch.allclose(dres.float(), rf.grad, atol=1e-2, rtol=2e-2)
+    if relu and res:
+        # the one-bit-per-element ReLU mask written by the forward gives exactly the results of masking by z
+        z2, stats2, mask = b200.bn_forward(y, _BN(c), r, relu, want_mask=True)
+        assert mask is not None and mask.numel() == rows * c // 8 and torch.equal(z2, z)
+        dy2, dres2, dgamma2, dbeta2 = b200.bn_backward(dz, y, None, stats2, relu, res, None, None, mask=mask)
+        assert torch.equal(dy2, dy) and torch.equal(dres2, dres) and torch.equal(dgamma2, dgamma) and torch.equal(dbeta2, dbeta)
 
 
 def test_bn_is_bitwise_reproducible():
