@@ -247,9 +247,13 @@ def broadcast_parameters(params, root_rank: int = 0) -> None:
     by_key = {}
     for t in tensors:
         by_key.setdefault((t.dtype, t.device), []).append(t)
+    ctx = _state.get("symm")
     for (_dt, _dev), ts in by_key.items():
         flat = torch.cat([t.detach().reshape(-1) for t in ts])
-        dist.broadcast(flat, src=root_rank)
+        if ctx is not None and flat.is_cuda and flat.dtype == torch.float32:
+            ctx.broadcast_tensor_(flat, root_rank)       # own NVLink broadcast kernel (K-BC), no NCCL
+        else:
+            dist.broadcast(flat, src=root_rank)
         off = 0
         with torch.no_grad():
             for t in ts:

@@ -259,6 +259,21 @@ class SymmetricContext:
         flat.copy_(view[: flat.numel()])
         return tensor
 
+    def broadcast_tensor_(self, tensor: torch.Tensor, root: int):
+        """Broadcast an ordinary fp32 CUDA tensor from ``root`` by staging it through symmetric scratch: the root
+        writes every peer's copy with the broadcast kernel (Horovod's broadcast_global_variables role)."""
+        flat = tensor.reshape(-1)
+        n = (flat.numel() + 3) // 4 * 4
+        need = n * 4
+        if self._scratch is None or self._scratch.nbytes < need:
+            self._scratch = self.alloc(max(need, 64 << 20), torch.uint8)
+        view = self._scratch.local_bytes[: n * 4].view(torch.float32)
+        if self.rank == root:
+            view[: flat.numel()].copy_(flat)
+        self.broadcast_(self._scratch, 0, n, root)      # offsets are in fp32 elements of the scratch allocation
+        flat.copy_(view[: flat.numel()])
+        return tensor
+
     def _count(self):
         self.launches += 1
         try:
