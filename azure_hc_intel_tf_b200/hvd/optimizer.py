@@ -266,6 +266,17 @@ class DistributedOptimizer:
                 p.grad = _physical_view(self.grad[s:s + n], p)
                 p.flat_index = i
         self.tracker = self.plan.tracker()
+        # Horovod's stall inspector: warn when a fused bucket has been in flight for too long (a rank that never
+        # reaches the collective). HOROVOD_STALL_CHECK_TIME_SECONDS (default 60; 0 disables) /
+        # HOROVOD_STALL_SHUTDOWN_TIME_SECONDS (default 0 = never abort), Horovod's own variable names.
+        import os as _os
+        warn_s = float(_os.environ.get("HOROVOD_STALL_CHECK_TIME_SECONDS", "60"))
+        abort_s = float(_os.environ.get("HOROVOD_STALL_SHUTDOWN_TIME_SECONDS", "0"))
+        self._stall = None
+        if warn_s > 0 and self.world > 1:
+            from .. import _native
+            lib = _native.host()
+            self._stall = (lib, lib.hvd_stall_start(self.tracker._h, min(5.0, warn_s / 2), warn_s, abort_s))
         self._cuda = self.grad.is_cuda
         self._comm_stream = torch.cuda.Stream(priority=-1) if self._cuda else None
         self._handles = []
@@ -411,6 +422,19 @@ class DistributedOptimizer:
         self._direct_seen = [False] * len(self.params)
         self.tracker.begin_step()
         return loss
+
+    def close(self):
+        """Stop the stall inspector thread (also called on garbage collection)."""
+        st = getattr(self, "_stall", None)
+        if st is not None and st[1]:
+            st[0].hvd_stall_stop(st[1])
+        self._stall = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def zero_grad(self, set_to_none: bool = False):
         # gradients are views into the fusion buffer: never detach them, just clear the buffer
