@@ -48,6 +48,7 @@ struct WgradParams {
   int kblocks_per_slice;
   int PQ, Q, stride_h, stride_w, base_h, base_w;
   int stages;
+  int dy_one_shot;       // dy planes of a stage come with one 3-D TMA instruction instead of one per 64 channels
   int atomic;            // 1: red.add into dw, 0: plain stores (to dw, or to this slice's workspace partial)
   float* dw;
   float* ws;             // when non-null: partial of slice s goes to ws + s * out_elems, a second kernel folds them
@@ -132,8 +133,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                                (uint16_t)fr);
           }
         }
-        for (int j = 0; j < nb; ++j)
-          tma_load_2d(sb + j * kBox, &map_dy, &bars->full[stage], n0 + j * 64, (int32_t)pix);
+        if (p.dy_one_shot) {
+          tma_load_3d(sb, &map_dy, &bars->full[stage], 0, (int32_t)pix, n0 / 64);
+        } else {
+          for (int j = 0; j < nb; ++j)
+            tma_load_2d(sb + j * kBox, &map_dy, &bars->full[stage], n0 + j * 64, (int32_t)pix);
+        }
         if (++stage == p.stages) {
           stage = 0;
           phase ^= 1;
@@ -348,7 +353,14 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
   if (tmap_im2col_nhwc(&mx, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
                        64, kBlockK))
     return -1;
-  if (tmap_tiled_2d(&mdy, dy, 2, (uint64_t)dy_ld, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, 64, kBlockK, true)) return -1;
+  const int nb_host = (p.block_n + 63) / 64;
+  p.dy_one_shot = 0;
+  if (dy_ld % 64 == 0 && g->k % 64 == 0 && nb_host > 1 &&
+      tmap_chunked_rows(&mdy, dy, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, (uint32_t)(g->k / 64), kBlockK, nb_host) == 0) {
+    p.dy_one_shot = 1;
+  } else if (tmap_tiled_2d(&mdy, dy, 2, (uint64_t)dy_ld, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, 64, kBlockK, true)) {
+    return -1;
+  }
   // several pixel slices: partials go to the workspace and are folded in a fixed order; without a workspace they
   // are combined with float atomics directly in dw (not bitwise reproducible)
   if (p.slices > 1 && workspace) {

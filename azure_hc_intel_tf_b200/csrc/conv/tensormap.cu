@@ -72,6 +72,25 @@ int tmap_tiled_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t i
   return 0;
 }
 
+int tmap_chunked_rows(CUtensorMap* map, const void* base, uint64_t rows, uint64_t row_stride_bytes, uint32_t chunks,
+                      uint32_t box_rows, uint32_t box_chunks) {
+  // [rows][chunks*64] bf16 viewed as {64, rows, chunks}: one box = box_chunks planes of [box_rows][64], i.e. the
+  // planes land back to back in shared memory ([chunk][row][128 B]) with a single TMA instruction
+  if (ensure() != 0) return -1;
+  cuuint64_t dims[3] = {64, rows, chunks};
+  cuuint64_t strides[2] = {row_stride_bytes, 128};
+  cuuint32_t box[3] = {64, box_rows, box_chunks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (chunked rows) failed (%d)", (int)r);
+    return -1;
+  }
+  return 0;
+}
+
 int tmap_im2col_nhwc(CUtensorMap* map, const void* base, int n, int h, int w, int c, int lower_w, int lower_h,
                      int upper_w, int upper_h, int stride_w, int stride_h, uint32_t channels_per_pixel,
                      uint32_t pixels_per_column) {

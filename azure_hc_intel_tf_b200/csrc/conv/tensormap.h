@@ -10,6 +10,11 @@ namespace b200 {
 int tmap_tiled_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t inner, uint64_t outer,
                   uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, bool swizzle128);
 
+// [rows][chunks*64] bf16 read as `box_chunks` consecutive 64-column planes of `box_rows` rows with ONE TMA instruction;
+// the planes land back to back in shared memory. Returns -1 (with b200_last_error) if the driver rejects the layout.
+int tmap_chunked_rows(CUtensorMap* map, const void* base, uint64_t rows, uint64_t row_stride_bytes, uint32_t chunks,
+                      uint32_t box_rows, uint32_t box_chunks);
+
 // im2col view of an NHWC bf16 tensor. lower/upper are the bounding-box corners of the filter's base pixel
 // (fprop: lower = -pad_lo, upper = pad_hi - (filter-1)); stride_* are the traversal strides.
 int tmap_im2col_nhwc(CUtensorMap* map, const void* base, int n, int h, int w, int c, int lower_w, int lower_h,
