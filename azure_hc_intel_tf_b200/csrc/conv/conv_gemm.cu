@@ -53,7 +53,13 @@ struct GemmParams {
   int scatter, sy, sx, H, W;
   float* col_stats;       // optional [gridDim.x*4][2][N]: per (CTA, 32-row group) running column sums / sums of squares
   int tma_store;          // epilogue stages bf16 tiles in shared memory and writes them with TMA bulk stores
+  // halo mode (3x3, stride 1, 64 reduction channels): an M tile is a 16 x 8 block of output pixels of one image; its
+  // 18 x 16 input halo is loaded once and the nine taps are shifted windows of it, the filter stays resident in smem
+  int halo, tiles_x, tiles_y, Himg, Wimg;
 };
+
+constexpr int kHaloRows = 18, kHaloCols = 16;
+constexpr int kHaloBytes = kHaloRows * kHaloCols * 128;     // 36 KiB: one 64-channel halo tile
 
 constexpr int kStageOutBytes = kBlockM * 64 * 2;   // one 128 x 64 bf16 output box, 128-byte swizzled
 constexpr int kOutBufs = 2;
@@ -63,6 +69,7 @@ struct __align__(8) Barriers {
   uint64_t empty[8];
   uint64_t tmem_full[kAccStages];
   uint64_t tmem_empty[kAccStages];
+  uint64_t bres;           // halo mode: the resident filter has landed
   uint32_t tmem_base;
 };
 
@@ -90,7 +97,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   // 1024-byte alignment is required by the 128-byte swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int b_bytes = p.block_n * kBlockK * 2;
-  const int stage_bytes = kABytes + b_bytes;
+  // halo mode: [resident filter: 9 taps x b_bytes][stages x halo tile]; otherwise [stages x (A tile, B tile)]
+  const int stage_bytes = p.halo ? kHaloBytes : kABytes + b_bytes;
+  uint8_t* const bres = smem;
+  if (p.halo) smem += 9 * b_bytes;
   uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;      // kOutBufs x 16 KiB when tma_store
   Barriers* bars = reinterpret_cast<Barriers*>(out_stage + (p.tma_store ? kOutBufs * kStageOutBytes : 0));
 
@@ -110,6 +120,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       mbar_init(&bars->tmem_full[i], 1);
       mbar_init(&bars->tmem_empty[i], 4);   // one arrive per epilogue warp
     }
+    mbar_init(&bars->bres, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<kTmemCols>(&bars->tmem_base);
@@ -120,7 +131,35 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   if (warp == 0) {
     // ================================================================ TMA producer
-    if (lane == 0) {
+    if (lane == 0 && p.halo) {
+      // filter of this CTA's N tile (gridDim.x is a multiple of num_n_tiles, so the N tile never changes): resident
+      const int nt0 = blockIdx.x % p.num_n_tiles, n00 = nt0 * p.block_n;
+      mbar_expect_tx(&bars->bres, (uint32_t)(9 * b_bytes));
+      for (int tap = 0; tap < 9; ++tap) {
+        if (!p.b_mn_major) {
+          tma_load_2d(bres + tap * b_bytes, &map_b, &bars->bres, tap * p.b_row_len, n00);
+        } else {
+          const int wtap = 8 - tap;                     // flipped taps for the backward-data direction
+          for (int j = 0; j < p.block_n / 64; ++j)
+            tma_load_2d(bres + tap * b_bytes + j * (kBlockK * 128), &map_b, &bars->bres, wtap * p.b_row_len + n00 + j * 64, 0);
+        }
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      const int per_img = p.tiles_x * p.tiles_y;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile / p.num_n_tiles;
+        const int img = mt / per_img, rem = mt - img * per_img;
+        const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+        mbar_wait(&bars->empty[stage], phase ^ 1);
+        mbar_expect_tx(&bars->full[stage], (uint32_t)kHaloBytes);
+        tma_load_4d(smem + (size_t)stage * stage_bytes, &map_a, &bars->full[stage], 0, tx * 8 - 1, ty * 16 - 1, img);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -171,11 +210,42 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
+    if (p.halo) mbar_wait(&bars->bres, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN);
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+      if (p.halo) {
+        mbar_wait(&bars->full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sh = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t sbr = smem_u32(bres);
+          for (int tap = 0; tap < 9; ++tap) {
+            const int r = tap / 3, s3 = tap - r * 3;
+            // A rows of this tap: halo pixel (ty + r, tx + s): 8-pixel groups 16 halo pixels (2 KiB) apart
+            const uint32_t a0 = sh + (uint32_t)((r * kHaloCols + s3) * 128);
+            const uint32_t b0 = sbr + (uint32_t)(tap * b_bytes);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k) {
+              // the 128-byte swizzle is a function of the shared-memory address itself (measured: a window that starts
+              // s rows into a TMA-written tile reads correctly with base offset 0), so a shifted start needs no fix-up
+              const uint64_t da = make_sdesc_sw128(a0 + k * 32, 16, kHaloCols * 128);
+              const uint64_t db = p.b_mn_major ? make_sdesc_sw128(b0 + k * 2048, kBlockK * 128, 1024)
+                                               : make_sdesc_sw128(b0 + k * 32, 16, 1024);
+              mma_bf16(d_tmem, da, db, idesc, (tap | k) != 0 ? 1u : 0u);
+            }
+          }
+          mma_commit(&bars->empty[stage]);
+          mma_commit(&bars->tmem_full[acc]);
+        }
+        __syncwarp();
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      for (int kb = 0; kb < (p.halo ? 0 : p.num_k_blocks); ++kb) {
         mbar_wait(&bars->full[stage], phase);
         tc_fence_after();
         if (lane == 0) {
@@ -232,6 +302,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if ((tile_i & 1) != grp) continue;
         const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
         const int n0 = nt * p.block_n;
+        int h_img = 0, h_y0 = 0, h_x0 = 0;           // halo mode: image and top-left output pixel of this tile
+        if (p.halo) {
+          const int per_img = p.tiles_x * p.tiles_y;
+          h_img = mt / per_img;
+          const int rem = mt - h_img * per_img;
+          h_y0 = (rem / p.tiles_x) * 16;
+          h_x0 = (rem % p.tiles_x) * 8;
+        }
         mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
@@ -282,7 +360,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           if (!p.scatter) {
             if (et == 0) {
-              tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
+              if (p.halo)
+                tma_store_4d(&map_out, buf, n0 + bx * 64, h_x0, h_y0, h_img);   // 16 x 8 pixels; clipped at the edges
+              else
+                tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
               tma_store_commit();
               store_pending = true;
             }
@@ -316,6 +397,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll 8
             for (int i = 0; i < 32; ++i) {
               const int row = qtr * 32 + i;
+              // halo tiles may hang over the image edge: those rows hold values that are never stored
+              if (p.halo && (h_y0 + (row >> 3) >= p.Himg || h_x0 + (row & 7) >= p.Wimg)) continue;
               const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4) + word * 4);
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
               s1a += f.x;
@@ -471,24 +554,33 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   // bf16 row-major outputs whose tile width is a multiple of 64 go out through shared memory + TMA bulk stores
   CUtensorMap mo;
   p.tma_store = (!p.out_fp32 && p.block_n % 64 == 0 && p.N % 8 == 0 && p.ldo % 8 == 0) ? 1 : 0;
-  if (p.tma_store && !p.scatter) {
+  if (p.halo) {
+    p.tma_store = 1;
+    if (tmap_nhwc_tile(&mo, p.out, p.M / (p.Himg * p.Wimg), p.Himg, p.Wimg, p.N, 64, 8, 16)) return -1;
+  } else if (p.tma_store && !p.scatter) {
     if (tmap_tiled_2d(&mo, p.out, 2, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldo * 2, 64, kBlockM, true)) return -1;
   } else {
     mo = ma;   // unused
   }
-  const int fixed = (int)sizeof(Barriers) + 1024 + (p.tma_store ? kOutBufs * kStageOutBytes : 0);
-  int stages = (227 * 1024 - fixed) / stage_bytes;
+  int fixed = (int)sizeof(Barriers) + 1024 + (p.tma_store ? kOutBufs * kStageOutBytes : 0);
+  int stage_bytes_eff = stage_bytes;
+  if (p.halo) {
+    fixed += 9 * p.block_n * kBlockK * 2;      // resident filter
+    stage_bytes_eff = kHaloBytes;
+  }
+  int stages = (227 * 1024 - fixed) / stage_bytes_eff;
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   p.stages = stages;
-  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  const size_t smem = (size_t)stages * stage_bytes_eff + fixed;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  if (p.halo) grid = grid / p.num_n_tiles * p.num_n_tiles;   // a CTA keeps one N tile's filter resident
   conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, mo, p);
   B200_LAUNCH_CHECK();
   return 0;
@@ -498,6 +590,31 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
 }  // namespace b200
 
 using namespace b200;
+
+static bool halo_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_HALO");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
+// 3x3 / stride 1 / pad 1 with exactly 64 reduction channels and 64 output columns: the halo kernel applies (with wider
+// outputs the generic im2col path, which covers all columns in one pass over the input, measured faster)
+static bool halo_shape(const b200_conv_geom* g, int red_ch, int out_ch) {
+  return halo_enabled() && g->r == 3 && g->s == 3 && g->stride_h == 1 && g->stride_w == 1 && g->pad_t == 1 &&
+         g->pad_l == 1 && g->pad_b == 1 && g->pad_r == 1 && red_ch == 64 && out_ch == 64 &&
+         g->h >= 16 && g->w >= 8;
+}
+
+static int64_t halo_grid(const b200_conv_geom* g, int out_ch) {
+  const int nt = out_ch / 64;
+  int64_t tiles = (int64_t)g->n * ((g->h + 15) / 16) * ((g->w + 7) / 8) * nt;
+  int64_t grid = tiles < kNumSMs ? tiles : kNumSMs;
+  return grid / nt * nt;
+}
+
 
 extern "C" int b200_conv_wgrad_supported(const b200_conv_geom* g);
 
@@ -526,6 +643,30 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   B200_CHECK_ARG(x && w && y && g, "conv_fprop: null pointer");
   B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin>=64, Cin%%8==0, Cout%%16==0)");
   CUtensorMap ma, mb;
+  if (halo_shape(g, g->c, g->k)) {
+    GemmParams p{};
+    p.halo = 1;
+    p.Himg = g->h;
+    p.Wimg = g->w;
+    p.tiles_y = (g->h + 15) / 16;
+    p.tiles_x = (g->w + 7) / 8;
+    p.M = g->n * g->h * g->w;
+    p.N = g->k;
+    p.block_n = 64;
+    p.num_m_tiles = g->n * p.tiles_y * p.tiles_x;
+    p.num_n_tiles = g->k / 64;
+    p.num_k_blocks = 1;
+    p.cchunks = 1;
+    p.R = p.S = 3;
+    p.b_row_len = g->c;
+    p.out = y;
+    p.ldo = g->k;
+    p.col_stats = col_stats;
+    if (tmap_nhwc_tile(&ma, x, g->n, g->h, g->w, g->c, 64, kHaloCols, kHaloRows)) return -1;
+    const int kd = 9 * g->c;
+    if (tmap_tiled_2d(&mb, w, 2, (uint64_t)kd, (uint64_t)g->k, (uint64_t)kd * 2, kBlockK, 64, true)) return -1;
+    return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+  }
   const int upper_w = g->pad_r - (g->s - 1), upper_h = g->pad_b - (g->r - 1);
   if (tmap_im2col_nhwc(&ma, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
                        kBlockK, kBlockM))
@@ -565,11 +706,13 @@ static int64_t grid_for_tiles(int64_t m, int n) {
 int64_t b200_conv_stats_rows(const b200_conv_geom* g) {
   // per CTA of the persistent grid: 8 scratch rows (epilogue group x 32-row group) + 1 folded row at the end
   if (!g) return -1;
+  if (halo_shape(g, g->c, g->k)) return halo_grid(g, g->k) * 9;
   return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 9;
 }
 
 int64_t b200_conv_stats_first_result_row(const b200_conv_geom* g) {
   if (!g) return -1;
+  if (halo_shape(g, g->c, g->k)) return halo_grid(g, g->k) * 8;
   return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 8;
 }
 
@@ -577,6 +720,30 @@ int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, cons
   B200_CHECK_ARG(dy && w && dx && g, "conv_dgrad: null pointer");
   B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_DGRAD), "conv_dgrad: unsupported geometry");
   CUtensorMap ma, mb;
+  if (halo_shape(g, g->k, g->c)) {
+    GemmParams p{};
+    p.halo = 1;
+    p.Himg = g->h;
+    p.Wimg = g->w;
+    p.tiles_y = (g->h + 15) / 16;
+    p.tiles_x = (g->w + 7) / 8;
+    p.M = g->n * g->h * g->w;
+    p.N = g->c;
+    p.block_n = 64;
+    p.num_m_tiles = g->n * p.tiles_y * p.tiles_x;
+    p.num_n_tiles = g->c / 64;
+    p.num_k_blocks = 1;
+    p.cchunks = 1;
+    p.R = p.S = 3;
+    p.b_mn_major = 1;
+    p.b_row_len = g->c;
+    p.out = dx;
+    p.ldo = g->c;
+    if (tmap_nhwc_tile(&ma, dy, g->n, g->p, g->q, g->k, 64, kHaloCols, kHaloRows)) return -1;
+    const int row = 9 * g->c;
+    if (tmap_tiled_2d(&mb, w, 2, (uint64_t)row, (uint64_t)g->k, (uint64_t)row * 2, 64, kBlockK, true)) return -1;
+    return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
+  }
   GemmParams p{};
   const bool strided = g->stride_h != 1 || g->stride_w != 1;
   if (!strided) {

@@ -91,6 +91,26 @@ int tmap_chunked_rows(CUtensorMap* map, const void* base, uint64_t rows, uint64_
   return 0;
 }
 
+int tmap_nhwc_tile(CUtensorMap* map, const void* base, int n, int h, int w, int c, uint32_t box_c, uint32_t box_w,
+                   uint32_t box_h) {
+  // plain tiled view of an NHWC bf16 tensor {C, W, H, N}; box = box_h x box_w pixels x box_c channels of one image.
+  // Coordinates may be negative / past the edge: those elements read as zero and are not written by stores.
+  if (ensure() != 0) return -1;
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
+  cuuint32_t box[4] = {box_c, box_w, box_h, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = g_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (nhwc tile) failed (%d): nhwc=%d,%d,%d,%d box=%u,%u,%u", (int)r, n, h, w, c, box_c,
+              box_w, box_h);
+    return -1;
+  }
+  return 0;
+}
+
 int tmap_im2col_nhwc(CUtensorMap* map, const void* base, int n, int h, int w, int c, int lower_w, int lower_h,
                      int upper_w, int upper_h, int stride_w, int stride_h, uint32_t channels_per_pixel,
                      uint32_t pixels_per_column) {

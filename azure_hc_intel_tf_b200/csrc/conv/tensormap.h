@@ -15,6 +15,10 @@ int tmap_tiled_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t i
 int tmap_chunked_rows(CUtensorMap* map, const void* base, uint64_t rows, uint64_t row_stride_bytes, uint32_t chunks,
                       uint32_t box_rows, uint32_t box_chunks);
 
+// Tiled view {C, W, H, N} of an NHWC bf16 tensor with a box of box_h x box_w pixels x box_c channels (128-byte swizzle).
+int tmap_nhwc_tile(CUtensorMap* map, const void* base, int n, int h, int w, int c, uint32_t box_c, uint32_t box_w,
+                   uint32_t box_h);
+
 // im2col view of an NHWC bf16 tensor. lower/upper are the bounding-box corners of the filter's base pixel
 // (fprop: lower = -pad_lo, upper = pad_hi - (filter-1)); stride_* are the traversal strides.
 int tmap_im2col_nhwc(CUtensorMap* map, const void* base, int n, int h, int w, int c, int lower_w, int lower_h,

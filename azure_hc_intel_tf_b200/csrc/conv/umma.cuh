@@ -89,6 +89,22 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
       : "memory");
 }
 
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int32_t c0, int32_t c1,
+                                            int32_t c2, int32_t c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int32_t c0, int32_t c1, int32_t c2,
+                                             int32_t c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
 // im2col mode, NHWC rank-4 tensor {C, W, H, N}: loads `pixelsPerColumn` consecutive output pixels starting at base
 // pixel (w, h, n) x `channelsPerPixel` channels starting at c, each read at filter offset (off_w, off_h).
 __device__ __forceinline__ void tma_load_im2col_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int32_t c,
@@ -197,5 +213,9 @@ __device__ __forceinline__ uint64_t make_sdesc_sw128(uint32_t smem_addr, uint32_
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+
+// Note on shifted windows: the swizzle XOR is taken from the shared-memory address bits themselves, so an operand that
+// starts a whole number of 128-byte rows into a tile written by TMA (1024-byte aligned) is described with the plain
+// descriptor above and base offset 0. Verified on B200 by the halo convolution kernel (conv_gemm.cu, halo mode).
 
 }  // namespace umma
