@@ -9,13 +9,16 @@
 namespace b200 {
 namespace {
 
+// Idx = uint32_t whenever the element count fits: 64-bit integer division in the index decode would otherwise cost
+// more than the memory traffic of these kernels.
+template <typename Idx>
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const b200_bf16* __restrict__ x, b200_bf16* __restrict__ y,
                                                           uint8_t* __restrict__ idx, b200_pool_geom g) {
   const int cv = g.c / 8;
-  const int64_t total = (int64_t)g.n * g.p * g.q * cv;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  const Idx total = (Idx)g.n * g.p * g.q * cv;
+  for (Idx i = (Idx)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (Idx)gridDim.x * blockDim.x) {
     int c8 = (int)(i % cv);
-    int64_t t = i / cv;
+    Idx t = i / cv;
     int q = (int)(t % g.q);
     t /= g.q;
     int p = (int)(t % g.p);
@@ -45,21 +48,22 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const b200_bf16* __res
         }
       }
     }
-    st8(y + i * 8, pack8(best));
+    st8(y + (int64_t)i * 8, pack8(best));
     uint2 pk;
     pk.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
     pk.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
-    *reinterpret_cast<uint2*>(idx + i * 8) = pk;
+    *reinterpret_cast<uint2*>(idx + (int64_t)i * 8) = pk;
   }
 }
 
+template <typename Idx>
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const b200_bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
                                                           b200_bf16* __restrict__ dx, b200_pool_geom g) {
   const int cv = g.c / 8;
-  const int64_t total = (int64_t)g.n * g.h * g.w * cv;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  const Idx total = (Idx)g.n * g.h * g.w * cv;
+  for (Idx i = (Idx)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (Idx)gridDim.x * blockDim.x) {
     int c8 = (int)(i % cv);
-    int64_t t = i / cv;
+    Idx t = i / cv;
     int w = (int)(t % g.w);
     t /= g.w;
     int h = (int)(t % g.h);
@@ -94,7 +98,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const b200_bf16* __res
         }
       }
     }
-    st8(dx + i * 8, pack8(acc));
+    st8(dx + (int64_t)i * 8, pack8(acc));
   }
 }
 
@@ -249,7 +253,10 @@ int b200_maxpool_fwd(const b200_bf16* x, b200_bf16* y, uint8_t* idx, const b200_
   if (int e = check_geom(g, "maxpool_fwd")) return e;
   B200_CHECK_ARG(x && y && idx, "maxpool_fwd: null pointer");
   int64_t total = (int64_t)g->n * g->p * g->q * (g->c / 8);
-  maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, idx, *g);
+  if (total < (1ll << 31))
+    maxpool_fwd_kernel<uint32_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, idx, *g);
+  else
+    maxpool_fwd_kernel<int64_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, idx, *g);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -258,7 +265,10 @@ int b200_maxpool_bwd(const b200_bf16* dy, const uint8_t* idx, b200_bf16* dx, con
   if (int e = check_geom(g, "maxpool_bwd")) return e;
   B200_CHECK_ARG(dy && dx && idx, "maxpool_bwd: null pointer");
   int64_t total = (int64_t)g->n * g->h * g->w * (g->c / 8);
-  maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, idx, dx, *g);
+  if (total < (1ll << 31))
+    maxpool_bwd_kernel<uint32_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, idx, dx, *g);
+  else
+    maxpool_bwd_kernel<int64_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, idx, dx, *g);
   B200_LAUNCH_CHECK();
   return 0;
 }
