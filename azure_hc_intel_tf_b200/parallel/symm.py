@@ -140,7 +140,7 @@ class SymmetricContext:
         self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(128 << 10)))
         # messages of at least this many bytes use the NVLS (in-switch reduction) kernel when the buffer has a
         # multicast mapping; -1 disables NVLS
-        self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(1 << 20)))
+        self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(8 << 20)))
         self.nvls_ok = None      # decided collectively at the first multicast allocation
         self.buffers: List[SymmBuffer] = []
         self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
