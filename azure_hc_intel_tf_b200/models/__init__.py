@@ -17,6 +17,8 @@ _REGISTRY = {
     "googlenet": zoo.GoogLeNet,
     "alexnet": zoo.AlexNet,
     "trivial": zoo.Trivial,
+    "lenet": zoo.LeNet,
+    "overfeat": zoo.Overfeat,
 }
 
 

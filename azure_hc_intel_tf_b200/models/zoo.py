@@ -56,6 +56,33 @@ class AlexNet(Sequential):
         self._finish(b, layers)
 
 
+class LeNet(Sequential):
+    """tf_cnn_benchmarks lenet5 (28x28 input)."""
+    image_size = 28
+    default_batch_size = 32
+
+    def __init__(self, cfg):
+        super().__init__(cfg)
+        self.name = "lenet"
+        b = ConvNetBuilder(cfg, 3, (28, 28))
+        layers = [b.conv(32, 5), b.mpool(2, 2), b.conv(64, 5), b.mpool(2, 2), b.reshape_flat(), b.affine(512)]
+        self._finish(b, layers)
+
+
+class Overfeat(Sequential):
+    image_size = 231
+    default_batch_size = 32
+
+    def __init__(self, cfg):
+        super().__init__(cfg)
+        self.name = "overfeat"
+        b = ConvNetBuilder(cfg, 3, (231, 231))
+        layers = [b.conv(96, 11, 4, "VALID"), b.mpool(2, 2), b.conv(256, 5, 1, "VALID"), b.mpool(2, 2),
+                  b.conv(512, 3), b.conv(1024, 3), b.conv(1024, 3), b.mpool(2, 2), b.reshape_flat(),
+                  b.affine(3072), b.dropout(), b.affine(4096), b.dropout()]
+        self._finish(b, layers)
+
+
 class Trivial(Sequential):
     image_size = 227
     default_batch_size = 32

@@ -223,8 +223,32 @@ def conv_block(x, m, relu, residual=None):
                             m.bias, residual, m, relu)
 
 
+class _BatchNorm(torch.autograd.Function):
+    """Standalone BatchNorm(+residual, +ReLU) for graphs that do not reach it through conv_block."""
+
+    @staticmethod
+    def forward(ctx, y, gamma, beta, residual, bn, relu):
+        y = nhwc(y)
+        if residual is not None:
+            residual = nhwc(residual)
+        z, stats, mask = bn_forward(y, bn, residual, relu, None, want_mask=True)
+        ctx.save_for_backward(y, mask, stats)
+        ctx.bn, ctx.relu, ctx.has_res, ctx.gamma, ctx.beta = bn, relu, residual is not None, gamma, beta
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        y, mask, stats = ctx.saved_tensors
+        gamma, beta = ctx.gamma, ctx.beta
+        g_gamma = _direct(gamma) if gamma.requires_grad else None
+        g_beta = _direct(beta)
+        dy, dres, dgamma, dbeta = bn_backward(nhwc(dz), y, None, stats, ctx.relu, ctx.has_res, g_gamma, g_beta, mask=mask)
+        return (dy, _deliver(gamma, g_gamma, dgamma) if gamma.requires_grad else None, _deliver(beta, g_beta, dbeta),
+                dres, None, None)
+
+
 def batch_norm(y, bn, relu, residual):
-    raise NotImplementedError("standalone batch_norm is only reached through conv_block on the b200 path")
+    return _BatchNorm.apply(y, bn.gamma, bn.beta, residual, bn, relu)
 
 
 # ------------------------------------------------------------------------------------ affine
@@ -347,7 +371,9 @@ def spatial_mean(x):
 
 
 def add_relu(a, b):
-    raise NotImplementedError("residual add is fused into conv_block(residual=...) on the b200 path")
+    """relu(a + b) outside a conv block (the residual add of ResNet is fused into conv_block(residual=...));
+    plain tensor ops: nothing in the model zoo reaches this on the kernel path."""
+    return torch.relu_(a + b)
 
 
 # ------------------------------------------------------------------------------------ loss / input
