@@ -31,6 +31,9 @@ constexpr int kBlockK = 64;          // pixels per pipeline stage
 constexpr int kBox = 64 * 128;       // one 64 x 64 bf16 TMA box, bytes
 constexpr int kTmemCols = 512;
 constexpr int kMaxStages = 6;
+constexpr int kHaloCols = 16, kHaloRows = 18;
+constexpr int kHaloBytes = kHaloRows * kHaloCols * 128;   // one 64-channel halo plane
+constexpr int kDyTileBytes = 128 * 128;                   // 16 x 8 pixels x 64 output channels
 
 struct WgradParams {
   int rows_total;        // R*S*C  (valid (tap,c) rows, = row length of dw)
@@ -49,6 +52,9 @@ struct WgradParams {
   int PQ, Q, stride_h, stride_w, base_h, base_w;
   int stages;
   int dy_one_shot;       // dy planes of a stage come with one 3-D TMA instruction instead of one per 64 channels
+  // halo mode (3x3, stride 1, pad 1): a k-block is a 16 x 8 tile of output pixels; the input halo of each 64-channel
+  // plane is loaded once and the taps are shifted windows of it. M index space = (channel plane, tap) in 64-row units.
+  int halo, tiles_x, tiles_y, cchunks;
   int atomic;            // 1: red.add into dw, 0: plain stores (to dw, or to this slice's workspace partial)
   float* dw;
   float* ws;             // when non-null: partial of slice s goes to ws + s * out_elems, a second kernel folds them
@@ -68,8 +74,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int nb = (p.block_n + 63) / 64;                 // dy boxes per stage
-  const int a_bytes = p.T * 2 * kBox;
-  const int stage_bytes = a_bytes + nb * kBox;
+  // halo mode: at most two channel planes are touched by the 2T consecutive (plane, tap) positions of one CTA
+  const int a_bytes = p.halo ? 2 * kHaloBytes : p.T * 2 * kBox;
+  const int stage_bytes = a_bytes + nb * (p.halo ? kDyTileBytes : kBox);
   WBarriers* bars = reinterpret_cast<WBarriers*>(smem + (size_t)p.stages * stage_bytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -103,7 +110,37 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
-  if (warp == 0) {
+  // halo mode: channel planes covered by this CTA's positions [2*tile0, 2*(tile0+tiles_here))
+  const int pos_lo = 2 * tile0;
+  int pos_hi = 2 * (tile0 + tiles_here) - 1;
+  if (pos_hi > 9 * p.cchunks - 1) pos_hi = 9 * p.cchunks - 1;
+  const int plane_lo = p.halo ? pos_lo / 9 : 0;
+  const int nplanes = p.halo ? pos_hi / 9 - plane_lo + 1 : 0;
+
+  if (warp == 0 && p.halo) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = (uint32_t)(nplanes * kHaloBytes + nb * kDyTileBytes);
+      const int per_img = p.tiles_x * p.tiles_y;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&bars->empty[stage], phase ^ 1);
+        uint8_t* sa = smem + (size_t)stage * stage_bytes;
+        uint8_t* sb = sa + a_bytes;
+        mbar_expect_tx(&bars->full[stage], tx_bytes);
+        const int img = kb / per_img, r2 = kb - img * per_img;
+        const int ty = r2 / p.tiles_x, tx = r2 - ty * p.tiles_x;
+        for (int pl = 0; pl < nplanes; ++pl)
+          tma_load_4d(sa + pl * kHaloBytes, &map_x, &bars->full[stage], (plane_lo + pl) * 64, tx * 8 - 1, ty * 16 - 1, img);
+        for (int j = 0; j < nb; ++j)
+          tma_load_4d(sb + j * kDyTileBytes, &map_dy, &bars->full[stage], n0 + j * 64, tx * 8, ty * 16, img);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
@@ -145,6 +182,42 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         }
       }
     }
+  } else if (warp == 1 && p.halo) {
+    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(&bars->full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t sb = sa + a_bytes;
+        for (int t = 0; t < tiles_here; ++t) {
+          // the two 64-row halves of M tile t: positions 2t and 2t+1 of the (plane, tap) space
+          const int p0 = 2 * (tile0 + t);
+          int p1 = p0 + 1;
+          if (p1 > 9 * p.cchunks - 1) p1 = p0;          // odd tail: second half is masked in the epilogue
+          const int pl0 = p0 / 9, tap0 = p0 - pl0 * 9, pl1 = p1 / 9, tap1 = p1 - pl1 * 9;
+          const uint32_t off0 = (uint32_t)((pl0 - plane_lo) * kHaloBytes + ((tap0 / 3) * kHaloCols + tap0 % 3) * 128);
+          const uint32_t off1 = (uint32_t)((pl1 - plane_lo) * kHaloBytes + ((tap1 / 3) * kHaloCols + tap1 % 3) * 128);
+          const uint32_t lbo = off1 > off0 ? off1 - off0 : 16;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {                 // 16 pixels per step = output rows 2k, 2k+1 of the tile
+            // shifted windows need no descriptor fix-up: the 128-byte swizzle follows the smem address (measured)
+            const uint64_t da = make_sdesc_sw128(sa + off0 + (uint32_t)(2 * k * kHaloCols * 128), lbo, kHaloCols * 128);
+            const uint64_t db = make_sdesc_sw128(sb + k * 2048, kDyTileBytes, 1024);
+            mma_bf16(tmem_base + (uint32_t)(t * p.block_n), da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+        }
+        mma_commit(&bars->empty[stage]);
+        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
   } else if (warp == 1) {
     const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
     int stage = 0;
@@ -180,8 +253,16 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     float* const outp = p.ws ? p.ws + (size_t)slice * p.out_elems : p.dw;
     for (int t = 0; t < tiles_here; ++t) {
       const int pidx = (tile0 + t) * 128 + lane_group * 32 + lane;   // position in the padded (tap, c') space
-      const int ptap = pidx / p.Cp, pc = pidx - ptap * p.Cp;
-      const bool valid = ptap < p.RS && pc < p.C;
+      int ptap = pidx / p.Cp, pc = pidx - ptap * p.Cp;
+      bool valid = ptap < p.RS && pc < p.C;
+      if (p.halo) {
+        // halo mode orders the M space (plane, tap): 64-row unit u = plane*9 + tap
+        const int u = pidx >> 6;
+        const int pl = u / 9;
+        ptap = u - pl * 9;
+        pc = pl * 64 + (pidx & 63);
+        valid = u < 9 * p.cchunks;
+      }
       const int idx = ptap * p.C + pc;                                // position in a dw row
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(t * p.block_n);
       for (int c = 0; c < p.block_n; c += 16) {
@@ -240,7 +321,24 @@ __global__ void __launch_bounds__(256) wgrad_fold_kernel(const float* __restrict
 
 constexpr int64_t kWorkspaceCap = 96ll << 20;
 
+bool wgrad_halo_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_HALO");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
 int plan(const b200_conv_geom* g, WgradParams& p) {
+  p.halo = (wgrad_halo_enabled() && g->r == 3 && g->s == 3 && g->stride_h == 1 && g->stride_w == 1 && g->pad_t == 1 &&
+            g->pad_l == 1 && g->pad_b == 1 && g->pad_r == 1 && g->c % 64 == 0 && g->c <= 128 && g->k % 64 == 0 &&
+            g->k <= 128 && g->h >= 16 && g->w >= 8)
+               ? 1
+               : 0;
+  p.cchunks = g->c / 64;
+  p.tiles_y = (g->h + 15) / 16;
+  p.tiles_x = (g->w + 7) / 8;
   p.C = g->c;
   p.Cp = (g->c + 63) / 64 * 64;
   p.S = g->s;
@@ -249,16 +347,16 @@ int plan(const b200_conv_geom* g, WgradParams& p) {
   p.kout = g->k;
   p.block_n = g->k >= 256 ? 256 : (g->k + 15) / 16 * 16;
   p.n_tiles = (g->k + p.block_n - 1) / p.block_n;
-  p.m_tiles_total = (p.RS * p.Cp + 127) / 128;
+  p.m_tiles_total = (p.RS * p.Cp + 127) / 128;   // same count in halo mode: 9 * cchunks 64-row units
   const int nb = (p.block_n + 63) / 64;
   int T = kTmemCols / p.block_n;
   // two pipeline stages must fit in ~200 KiB: (T*16 KiB + nb*8 KiB) * 2
-  while (T > 1 && (T * 2 * kBox + nb * kBox) * 2 > 200 * 1024) --T;
+  while (!p.halo && T > 1 && (T * 2 * kBox + nb * kBox) * 2 > 200 * 1024) --T;
   if (T > p.m_tiles_total) T = p.m_tiles_total;
   p.T = T;
   p.m_groups = (p.m_tiles_total + T - 1) / T;
   p.pix_total = (int64_t)g->n * g->p * g->q;
-  p.kblocks_total = (int)((p.pix_total + kBlockK - 1) / kBlockK);
+  p.kblocks_total = p.halo ? g->n * p.tiles_y * p.tiles_x : (int)((p.pix_total + kBlockK - 1) / kBlockK);
   const int groups = p.m_groups * p.n_tiles;
   p.out_elems = (int64_t)g->k * p.rows_total;
   // one wave of CTAs: as many pixel slices as fit next to the output groups, bounded by the work per slice and by
@@ -273,7 +371,7 @@ int plan(const b200_conv_geom* g, WgradParams& p) {
   p.kblocks_per_slice = (p.kblocks_total + slices - 1) / slices;
   p.slices = (p.kblocks_total + p.kblocks_per_slice - 1) / p.kblocks_per_slice;
   p.atomic = p.slices > 1;
-  const int stage_bytes = T * 2 * kBox + nb * kBox;
+  const int stage_bytes = p.halo ? 2 * kHaloBytes + nb * kDyTileBytes : T * 2 * kBox + nb * kBox;
   int stages = (200 * 1024) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
@@ -350,12 +448,17 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
   p.dw = dw;
   CUtensorMap mx, mdy;
   const int upper_w = g->pad_r - (g->s - 1), upper_h = g->pad_b - (g->r - 1);
-  if (tmap_im2col_nhwc(&mx, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w, g->stride_h,
-                       64, kBlockK))
+  if (p.halo) {
+    if (tmap_nhwc_tile(&mx, x, g->n, g->h, g->w, g->c, 64, kHaloCols, kHaloRows)) return -1;
+    if (tmap_nhwc_tile(&mdy, dy, g->n, g->p, g->q, dy_ld, 64, 8, 16)) return -1;
+  } else if (tmap_im2col_nhwc(&mx, x, g->n, g->h, g->w, g->c, -g->pad_l, -g->pad_t, upper_w, upper_h, g->stride_w,
+                              g->stride_h, 64, kBlockK))
     return -1;
   const int nb_host = (p.block_n + 63) / 64;
   p.dy_one_shot = 0;
-  if (dy_ld % 64 == 0 && g->k % 64 == 0 && nb_host > 1 &&
+  if (p.halo) {
+    // maps were built above
+  } else if (dy_ld % 64 == 0 && g->k % 64 == 0 && nb_host > 1 &&
       tmap_chunked_rows(&mdy, dy, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, (uint32_t)(g->k / 64), kBlockK, nb_host) == 0) {
     p.dy_one_shot = 1;
   } else if (tmap_tiled_2d(&mdy, dy, 2, (uint64_t)dy_ld, (uint64_t)p.pix_total, (uint64_t)dy_ld * 2, 64, kBlockK, true)) {
@@ -370,7 +473,8 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
     B200_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)p.out_elems, st));
   }
   const int nb = (p.block_n + 63) / 64;
-  const size_t smem = (size_t)p.stages * (p.T * 2 * kBox + nb * kBox) + sizeof(WBarriers) + 1024;
+  const size_t smem = (size_t)p.stages * (p.halo ? 2 * kHaloBytes + nb * kDyTileBytes : p.T * 2 * kBox + nb * kBox) +
+                      sizeof(WBarriers) + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
