@@ -11,11 +11,13 @@
 //           read as an MN-major operand with the taps flipped - no transposed weight copy is made
 //   gemm  : A[M,K] row-major, B[N,K] row-major (both TMA tiled)
 //
-// CTA layout (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
-// warps 2..5 and 6..9 = two epilogue groups (TMEM -> registers -> bf16 -> swizzled smem -> TMA bulk store, or a
-// cooperative scatter for strided dgrad). Pipelines: smem ring (full/empty mbarriers) between TMA and MMA; two TMEM
-// accumulator stages (tmem_full/tmem_empty), one owned by each epilogue group, so the epilogues of tiles i and i+1
-// overlap each other and the main loop of tile i+2.
+// CTA layout (576 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..17 = four epilogue groups of four warps (TMEM -> registers -> bf16 -> swizzled smem -> TMA bulk store, or
+// a cooperative scatter for strided dgrad). Pipelines: smem ring (full/empty mbarriers) between TMA and MMA; two TMEM
+// accumulator stages (tmem_full/tmem_empty). Groups 2a and 2a+1 drain stage a together, each taking half of the
+// tile's 64-column boxes, so the epilogues of tiles i and i+1 overlap each other and the main loop of tile i+2 and
+// every SM sub-partition has four epilogue warps to hide the TMEM-load / shared-memory latencies behind each other
+// (with two groups the memory-bound 1x1 layers were epilogue-latency-bound at ~40% of DRAM bandwidth).
 #include "b200conv.h"
 #include "common.cuh"
 #include "conv/tensormap.h"
@@ -29,7 +31,7 @@ using namespace umma;
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;                    // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kMaxBlockN = 256;
-constexpr int kThreads = 320;                  // warp 0 TMA, warp 1 MMA, warps 2-5 and 6-9: two epilogue groups
+constexpr int kThreads = 576;                  // warp 0 TMA, warp 1 MMA, warps 2-17: four epilogue groups
 constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kAccStages = 2;
 constexpr int kTmemCols = 512;
@@ -56,13 +58,16 @@ struct GemmParams {
   // halo mode (3x3, stride 1, 64 reduction channels): an M tile is a 16 x 8 block of output pixels of one image; its
   // 18 x 16 input halo is loaded once and the nine taps are shifted windows of it, the filter stays resident in smem
   int halo, tiles_x, tiles_y, Himg, Wimg;
+  // resident-filter mode (generic path): the whole [K][block_n] filter slice of this CTA's N tile stays in shared
+  // memory for the life of the CTA, so the pipeline only streams the activation operand
+  int b_resident;
 };
 
 constexpr int kHaloRows = 18, kHaloCols = 16;
 constexpr int kHaloBytes = kHaloRows * kHaloCols * 128;     // 36 KiB: one 64-channel halo tile
 
 constexpr int kStageOutBytes = kBlockM * 64 * 2;   // one 128 x 64 bf16 output box, 128-byte swizzled
-constexpr int kOutBufs = 2;
+constexpr int kOutBufs = 4;                        // one staging box per epilogue group
 
 struct __align__(8) Barriers {
   uint64_t full[8];
@@ -98,9 +103,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int b_bytes = p.block_n * kBlockK * 2;
   // halo mode: [resident filter: 9 taps x b_bytes][stages x halo tile]; otherwise [stages x (A tile, B tile)]
-  const int stage_bytes = p.halo ? kHaloBytes : kABytes + b_bytes;
+  const int stage_bytes = p.halo ? kHaloBytes : (p.b_resident ? kABytes : kABytes + b_bytes);
   uint8_t* const bres = smem;
   if (p.halo) smem += 9 * b_bytes;
+  if (p.b_resident) smem += p.num_k_blocks * b_bytes;
   uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;      // kOutBufs x 16 KiB when tma_store
   Barriers* bars = reinterpret_cast<Barriers*>(out_stage + (p.tma_store ? kOutBufs * kStageOutBytes : 0));
 
@@ -118,7 +124,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     for (int i = 0; i < kAccStages; ++i) {
       mbar_init(&bars->tmem_full[i], 1);
-      mbar_init(&bars->tmem_empty[i], 4);   // one arrive per epilogue warp
+      // one arrive per epilogue warp that drains the stage: both groups of the pair when the tile has >= 2 boxes
+      mbar_init(&bars->tmem_empty[i], (p.tma_store && p.block_n >= 128) ? 8 : 4);
     }
     mbar_init(&bars->bres, 1);
     fence_barrier_init();
@@ -160,6 +167,23 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
       }
     } else if (lane == 0) {
+      if (p.b_resident) {
+        // gridDim.x is a multiple of num_n_tiles here, so this CTA only ever sees one N tile
+        const int n00 = (blockIdx.x % p.num_n_tiles) * p.block_n;
+        mbar_expect_tx(&bars->bres, (uint32_t)(p.num_k_blocks * b_bytes));
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          const int tap = kb / p.cchunks, cc = kb - tap * p.cchunks;
+          uint8_t* sb = bres + kb * b_bytes;
+          if (!p.b_mn_major) {
+            tma_load_2d(sb, &map_b, &bars->bres, p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n00);
+          } else {
+            const int r = tap / p.S, s2 = tap - r * p.S;
+            const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s2);
+            for (int j = 0; j < p.block_n / 64; ++j)
+              tma_load_2d(sb + j * (kBlockK * 128), &map_b, &bars->bres, wtap * p.b_row_len + n00 + j * 64, cc * kBlockK);
+          }
+        }
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -185,7 +209,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           } else {
             tma_load_2d(sa, &map_a, &bars->full[stage], kb * kBlockK, m0);
           }
-          if (!p.b_mn_major) {
+          if (p.b_resident) {
+            // filter already in shared memory
+          } else if (!p.b_mn_major) {
             // K-major weights [Cout][(r,s),Cin]: chunk cc of tap (r,s). With Cin % 64 != 0 the last chunk of a tap
             // runs into the next tap's channels; the matching A columns were zero-filled by TMA, so they add nothing.
             tma_load_2d(sb, &map_b, &bars->full[stage], p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n0);
@@ -210,7 +236,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    if (p.halo) mbar_wait(&bars->bres, 0);
+    if (p.halo || p.b_resident) mbar_wait(&bars->bres, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
@@ -250,7 +276,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tc_fence_after();
         if (lane == 0) {
           const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
-          const uint32_t sb = sa + kABytes;
+          const uint32_t sb = p.b_resident ? smem_u32(bres) + (uint32_t)(kb * b_bytes) : sa + kABytes;
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             const uint64_t da = make_sdesc_sw128(sa + k * 32, 16, 1024);
@@ -273,24 +299,28 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else {
-    // ================================================================ epilogue (warps 2..5 = group 0, 6..9 = group 1)
+    // ================================================================ epilogue (warps 2..17 = groups 0..3)
     const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
-    const int grp = (warp - 2) >> 2;            // group g owns TMEM accumulator stage g and tiles g, g+2, ... of this CTA
-    const int acc = grp;
+    const int grp = (warp - 2) >> 2;            // 0..3
+    const int acc = grp >> 1;                   // pair a = groups 2a, 2a+1 owns accumulator stage a: tiles a, a+2, ...
+    const int half = grp & 1;                   // which half of the tile's boxes this group drains
     uint32_t acc_phase = 0;
-    const int eg = threadIdx.x - 64 - grp * 128;    // 0..127 within the group
     if (p.col_stats) {
-      // running statistics of this (CTA, group): four 32-row-group rows of [2][N] floats, zeroed here (no memset launch)
-      float4* z = reinterpret_cast<float4*>(p.col_stats + ((size_t)blockIdx.x * 2 + grp) * 4 * 2 * p.N);
+      // running statistics of this (CTA, pair): four 32-row-group rows of [2][N] floats, zeroed here (no memset launch)
+      const int eg = threadIdx.x - 64 - acc * 256;    // 0..255 within the pair
+      float4* z = reinterpret_cast<float4*>(p.col_stats + ((size_t)blockIdx.x * 2 + acc) * 4 * 2 * p.N);
       const int n4 = 4 * 2 * p.N / 4;
-      for (int i = eg; i < n4; i += 128) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = eg; i < n4; i += 256) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       __threadfence_block();
-      asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+      asm volatile("bar.sync %0, 256;" ::"r"(6 + acc) : "memory");
     }
     if (p.tma_store) {
       // ---- staged path: TMEM -> registers -> bf16 -> swizzled shared memory -> TMA bulk store (or cooperative
       //      scatter); BatchNorm statistics are taken from the staged (stored) values with conflict-free reads.
       const int et = threadIdx.x - 64 - grp * 128;   // 0..127 within the group
+      const int nboxes = p.block_n / 64;
+      // boxes [bx0, bx1) of every tile of this pair are this group's; a one-box tile leaves the second group idle
+      const int bx0 = half ? (nboxes + 1) / 2 : 0, bx1 = half ? nboxes : (nboxes + 1) / 2;
       const int r_in_tile = lane_group * 32 + lane;
       const int cp = et & 31;                   // column pair handled for statistics
       const int qtr = et >> 5;                  // 32-row group handled for statistics
@@ -298,8 +328,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int bar_id = 1 + grp;
       bool store_pending = false;
       int tile_i = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_i) {
-        if ((tile_i & 1) != grp) continue;
+      for (int tile = blockIdx.x; tile < num_tiles && bx0 < bx1; tile += gridDim.x, ++tile_i) {
+        if ((tile_i & 1) != acc) continue;
         const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
         const int n0 = nt * p.block_n;
         int h_img = 0, h_y0 = 0, h_x0 = 0;           // halo mode: image and top-left output pixel of this tile
@@ -313,12 +343,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
-        const int nboxes = p.block_n / 64;
-        for (int bx = 0; bx < nboxes; ++bx) {
+        for (int bx = bx0; bx < bx1; ++bx) {
           // this CTA-group's running column statistics for (row group qtr, column pair cp) of this box: fetched now,
           // the latency hides behind the TMEM loads below; only this thread ever touches these addresses
           float* const st_dst = (p.col_stats && n0 + bx * 64 + cp * 2 < p.N)
-                                    ? p.col_stats + (((size_t)blockIdx.x * 2 + grp) * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
+                                    ? p.col_stats + (((size_t)blockIdx.x * 2 + acc) * 4 + qtr) * 2 * p.N + n0 + bx * 64 + cp * 2
                                     : nullptr;
           float2 old1 = make_float2(0.f, 0.f), old2 = make_float2(0.f, 0.f);
           if (st_dst) {
@@ -350,7 +379,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
           for (int chunk = 0; chunk < 8; ++chunk)
             *reinterpret_cast<uint4*>(buf + r_in_tile * 128 + ((chunk ^ (r_in_tile & 7)) << 4)) = pk[chunk];
-          if (bx == nboxes - 1) {
+          if (bx == bx1 - 1) {
             // all of this tile's accumulators are out of TMEM: hand the stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
@@ -415,8 +444,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       if (et == 0 && store_pending) tma_store_wait<0>();
     } else {
       int tile_i = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_i) {
-        if ((tile_i & 1) != grp) continue;
+      // narrow / fp32 outputs: the first group of each pair drains the whole tile
+      for (int tile = blockIdx.x; tile < num_tiles && half == 0; tile += gridDim.x, ++tile_i) {
+        if ((tile_i & 1) != acc) continue;
         const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
         const int row = mt * kBlockM + lane_group * 32 + lane;
         const int n0 = nt * p.block_n;
@@ -465,7 +495,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
             if (lane < 16) {
               const int col = lane;
-              float* dst = p.col_stats + (((size_t)blockIdx.x * 2 + grp) * 4 + lane_group) * 2 * p.N + n0 + c + col;
+              float* dst = p.col_stats + (((size_t)blockIdx.x * 2 + acc) * 4 + lane_group) * 2 * p.N + n0 + c + col;
               dst[0] += s1[0];
               dst[p.N] += s2[0];
             }
@@ -508,14 +538,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
     if (p.col_stats) {
-      // fold this CTA's 8 running rows (2 groups x 4 row groups) into one row of the compact result region that
+      // fold this CTA's 8 running rows (2 pairs x 4 row groups) into one row of the compact result region that
       // follows the scratch rows, in a fixed order; bn_finalize_partials then reads one row per CTA
       __threadfence_block();
-      asm volatile("bar.sync 3, 256;" ::: "memory");
-      const int e8 = threadIdx.x - 64;          // 0..255
+      asm volatile("bar.sync 5, 512;" ::: "memory");
+      const int e8 = threadIdx.x - 64;          // 0..511
       const float* src = p.col_stats + (size_t)blockIdx.x * 8 * 2 * p.N;
       float* dst = p.col_stats + (size_t)gridDim.x * 8 * 2 * p.N + (size_t)blockIdx.x * 2 * p.N;
-      for (int i = e8; i < 2 * p.N; i += 256) {
+      for (int i = e8; i < 2 * p.N; i += 512) {
         float a = 0.0f;
 #pragma unroll
         for (int rrow = 0; rrow < 8; ++rrow) a += __ldcg(src + (size_t)rrow * 2 * p.N + i);
@@ -564,9 +594,21 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   }
   int fixed = (int)sizeof(Barriers) + 1024 + (p.tma_store ? kOutBufs * kStageOutBytes : 0);
   int stage_bytes_eff = stage_bytes;
+  const int tiles_all = p.num_m_tiles * p.num_n_tiles;
   if (p.halo) {
     fixed += 9 * p.block_n * kBlockK * 2;      // resident filter
     stage_bytes_eff = kHaloBytes;
+  } else {
+    // keep the filter slice resident when it is small and every CTA sticks to one N tile (memory-bound 1x1 layers:
+    // the per-tile filter reload would otherwise be most of the L2 traffic)
+    static const bool res_ok = !(getenv("B200_CONV_BRES") && getenv("B200_CONV_BRES")[0] == '0');
+    const int64_t bres_bytes = (int64_t)p.num_k_blocks * p.block_n * kBlockK * 2;
+    const int grid0 = tiles_all < kNumSMs ? tiles_all : kNumSMs;
+    p.b_resident = (res_ok && bres_bytes <= 96 * 1024 && p.num_m_tiles >= 4 * kNumSMs && grid0 % p.num_n_tiles == 0) ? 1 : 0;
+    if (p.b_resident) {
+      fixed += (int)bres_bytes;
+      stage_bytes_eff = kABytes;
+    }
   }
   int stages = (227 * 1024 - fixed) / stage_bytes_eff;
   if (stages > 8) stages = 8;
