@@ -294,27 +294,45 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   }
 }
 
-// dw[e] = sum over slices of ws[s][e], in slice order (bitwise reproducible).
+// dw[e] = sum over slices of ws[s][e] in a fixed order (bitwise reproducible): a block is 32 float4 columns x 8 slice
+// lanes; lane y adds slices y, y+8, ... in order, then the eight lane sums are added in lane order. The slice lanes
+// keep enough loads in flight that small filters (few columns, many slices) are not latency-bound.
 __global__ void __launch_bounds__(256) wgrad_fold_kernel(const float* __restrict__ ws, float* __restrict__ dw,
                                                          int64_t n, int slices) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
-  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+  __shared__ float4 part[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t i = ((int64_t)blockIdx.x * 32 + tx) * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i + 4 <= n) {
+#pragma unroll 4
+    for (int s2 = ty; s2 < slices; s2 += 8) {
+      const float4 b = __ldcs(reinterpret_cast<const float4*>(ws + (size_t)s2 * n + i));
+      a.x += b.x;
+      a.y += b.y;
+      a.z += b.z;
+      a.w += b.w;
+    }
+  } else if (i < n) {
+    float* av = &a.x;
+    for (int j = 0; j < (int)(n - i); ++j)
+      for (int s2 = ty; s2 < slices; s2 += 8) av[j] += ws[(size_t)s2 * n + i + j];
+  }
+  part[ty][tx] = a;
+  __syncthreads();
+  if (ty == 0 && i < n) {
+#pragma unroll
+    for (int y = 1; y < 8; ++y) {
+      const float4 b = part[y][tx];
+      a.x += b.x;
+      a.y += b.y;
+      a.z += b.z;
+      a.w += b.w;
+    }
     if (i + 4 <= n) {
-      float4 a = __ldcs(reinterpret_cast<const float4*>(ws + i));
-      for (int s2 = 1; s2 < slices; ++s2) {
-        const float4 b = __ldcs(reinterpret_cast<const float4*>(ws + (size_t)s2 * n + i));
-        a.x += b.x;
-        a.y += b.y;
-        a.z += b.z;
-        a.w += b.w;
-      }
       *reinterpret_cast<float4*>(dw + i) = a;
     } else {
-      for (int64_t j = i; j < n; ++j) {
-        float a = ws[j];
-        for (int s2 = 1; s2 < slices; ++s2) a += ws[(size_t)s2 * n + j];
-        dw[j] = a;
-      }
+      const float* av = &a.x;
+      for (int j = 0; j < (int)(n - i); ++j) dw[i + j] = av[j];
     }
   }
 }
@@ -485,7 +503,7 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
   B200_LAUNCH_CHECK();
   if (p.ws) {
     const int64_t vec = (p.out_elems + 3) / 4;
-    wgrad_fold_kernel<<<grid_for(vec, 256, 4), 256, 0, st>>>(p.ws, dw, p.out_elems, p.slices);
+    wgrad_fold_kernel<<<(unsigned)((vec + 31) / 32), 256, 0, st>>>(p.ws, dw, p.out_elems, p.slices);
     B200_LAUNCH_CHECK();
   }
   return 0;

@@ -20,3 +20,15 @@ for _ in range(3):
     dw = conv_umma.wgrad(x, dy, m)
 torch.cuda.synchronize()
 print("ok", y.shape, dw.shape)
+if len(sys.argv) > 7 and sys.argv[7] == "prof":
+    from torch.profiler import profile, ProfilerActivity
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as pr:
+        for _ in range(5):
+            y, st = conv_umma.fprop(x, w, m, want_stats=True)
+            if conv_umma.supports_dgrad(dy, w, m, x.shape):
+                dx = conv_umma.dgrad(dy, w, m, x.shape)
+            dw = conv_umma.wgrad(x, dy, m)
+        torch.cuda.synchronize()
+    for e in pr.key_averages():
+        if e.device_time_total > 0:
+            print(f"{e.key[:70]:70s} n={e.count:3d} avg={e.device_time_total / e.count:8.1f} us")
