@@ -26,7 +26,7 @@ namespace {
 
 using namespace umma;
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;        // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kBlockK = 64;          // pixels per pipeline stage
 constexpr int kBox = 64 * 128;       // one 64 x 64 bf16 TMA box, bytes
 constexpr int kTmemCols = 512;
@@ -246,7 +246,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
       }
     }
   } else {
-    const int lane_group = warp & 3;
+    const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
+    const int col_half = (warp - 2) >> 2;       // eight epilogue warps: two per lane group
     mbar_wait_backoff(&bars->tmem_full, 0);
     tc_fence_after();
     const size_t ld = (size_t)p.rows_total;       // dw[k][rows_total]
@@ -265,21 +266,30 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
       }
       const int idx = ptap * p.C + pc;                                // position in a dw row
       const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(t * p.block_n);
-      for (int c = 0; c < p.block_n; c += 16) {
+      // the two warps of a lane group take alternate 16-column chunks
+      for (int c = col_half * 16; c < p.block_n; c += 32) {
         uint32_t r[16];
         tmem_ld_x16(t_row + (uint32_t)c, r);
         tmem_ld_wait();
-        if (valid) {
+        if (!valid) continue;
+        float* d = outp + (size_t)(n0 + c) * ld + idx;
+        if (!p.atomic && n0 + c + 16 <= p.kout) {
+          // fast path: 16 plain stores, one pointer bump each (a warp's store covers one 128-byte line)
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int ko = n0 + c + j;
-            if (ko < p.kout) {
-              float* dst = outp + (size_t)ko * ld + idx;
+            *d = __uint_as_float(r[j]);
+            d += ld;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (n0 + c + j < p.kout) {
               if (p.atomic)
-                asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dst), "f"(__uint_as_float(r[j])) : "memory");
+                asm volatile("red.global.add.f32 [%0], %1;" ::"l"(d), "f"(__uint_as_float(r[j])) : "memory");
               else
-                *dst = __uint_as_float(r[j]);
+                *d = __uint_as_float(r[j]);
             }
+            d += ld;
           }
         }
       }
