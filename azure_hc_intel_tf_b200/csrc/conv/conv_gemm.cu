@@ -61,6 +61,8 @@ struct GemmParams {
   // resident-filter mode (generic path): the whole [K][block_n] filter slice of this CTA's N tile stays in shared
   // memory for the life of the CTA, so the pipeline only streams the activation operand
   int b_resident;
+  // debug (B200_CONV_TRACE=1): CTA 0 accumulates the cycles its roles spend waiting on each barrier class
+  long long* trace;
 };
 
 constexpr int kHaloRows = 18, kHaloCols = 16;
@@ -95,6 +97,20 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_
   reinterpret_cast<uint4*>(dst)[1] = v1;
 }
 
+__device__ long long g_trace[8];
+
+// timed barrier wait for the trace: slot 0 producer<-empty, 1 MMA<-tmem_empty, 2 MMA<-full, 3 epilogue<-tmem_full
+#define TRACED_WAIT(slot, call)                                   \
+  do {                                                            \
+    if (tr) {                                                     \
+      const long long t0_ = clock64();                            \
+      call;                                                       \
+      if (lane == 0) tr_acc[slot] += clock64() - t0_;             \
+    } else {                                                      \
+      call;                                                       \
+    }                                                             \
+  } while (0)
+
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_out, const GemmParams p) {
@@ -113,6 +129,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const bool tr = p.trace != nullptr && blockIdx.x == 0;
+  long long tr_acc[4] = {0, 0, 0, 0};
+  const long long tr_start = tr ? clock64() : 0;
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_a);
@@ -198,7 +217,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           qw = (rem - pp * p.Q) * p.stride_w + p.base_w;
         }
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(&bars->empty[stage], phase ^ 1);
+          TRACED_WAIT(0, mbar_wait(&bars->empty[stage], phase ^ 1));
           uint8_t* sa = smem + (size_t)stage * stage_bytes;
           uint8_t* sb = sa + kABytes;
           mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
@@ -238,7 +257,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t acc_phase = 0;
     if (p.halo || p.b_resident) mbar_wait(&bars->bres, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+      TRACED_WAIT(1, mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1));
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN);
       if (p.halo) {
@@ -272,7 +291,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
       }
       for (int kb = 0; kb < (p.halo ? 0 : p.num_k_blocks); ++kb) {
-        mbar_wait(&bars->full[stage], phase);
+        TRACED_WAIT(2, mbar_wait(&bars->full[stage], phase));
         tc_fence_after();
         if (lane == 0) {
           const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
@@ -340,7 +359,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           h_y0 = (rem / p.tiles_x) * 16;
           h_x0 = (rem % p.tiles_x) * 8;
         }
-        mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
+        TRACED_WAIT(3, mbar_wait_backoff(&bars->tmem_full[acc], acc_phase));
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
         for (int bx = bx0; bx < bx1; ++bx) {
@@ -556,6 +575,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  if (tr && lane == 0) {
+    // slots 0..2 have one writer each; slot 3 = epilogue warp 2 (group 0, lane group 2); slot 4 = CTA lifetime
+    if (warp == 0) p.trace[0] = tr_acc[0];
+    if (warp == 1) {
+      p.trace[1] = tr_acc[1];
+      p.trace[2] = tr_acc[2];
+    }
+    if (warp == 2) p.trace[3] = tr_acc[3];
+    if (warp == 3) p.trace[4] = clock64() - tr_start;
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem_base);
@@ -604,7 +633,11 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
     static const bool res_ok = !(getenv("B200_CONV_BRES") && getenv("B200_CONV_BRES")[0] == '0');
     const int64_t bres_bytes = (int64_t)p.num_k_blocks * p.block_n * kBlockK * 2;
     const int grid0 = tiles_all < kNumSMs ? tiles_all : kNumSMs;
-    p.b_resident = (res_ok && bres_bytes <= 96 * 1024 && p.num_m_tiles >= 4 * kNumSMs && grid0 % p.num_n_tiles == 0) ? 1 : 0;
+    static const int res_max_kb = getenv("B200_CONV_BRES_KB") ? atoi(getenv("B200_CONV_BRES_KB")) : 96;
+    // at least two 16 KiB activation stages must still fit next to the resident slice
+    const bool fits = fixed + bres_bytes + 2 * kABytes <= 227 * 1024;
+    p.b_resident = (res_ok && fits && bres_bytes <= (int64_t)res_max_kb * 1024 && p.num_m_tiles >= 2 * kNumSMs &&
+                    grid0 % p.num_n_tiles == 0) ? 1 : 0;
     if (p.b_resident) {
       fixed += (int)bres_bytes;
       stage_bytes_eff = kABytes;
@@ -623,8 +656,26 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   int grid = tiles < kNumSMs ? tiles : kNumSMs;
   if (p.halo) grid = grid / p.num_n_tiles * p.num_n_tiles;   // a CTA keeps one N tile's filter resident
+  static const bool trace_on = getenv("B200_CONV_TRACE") && getenv("B200_CONV_TRACE")[0] == '1';
+  static long long* trace_buf = nullptr;
+  if (trace_on) {
+    // debug only: synchronous; never on in a benchmark or under graph capture
+    if (!trace_buf) B200_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&trace_buf), g_trace));
+    B200_CUDA(cudaMemsetAsync(trace_buf, 0, 8 * sizeof(long long), st));
+    p.trace = trace_buf;
+  }
   conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, mo, p);
   B200_LAUNCH_CHECK();
+  if (trace_on) {
+    long long h[8];
+    B200_CUDA(cudaStreamSynchronize(st));
+    B200_CUDA(cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr,
+            "[conv trace] M=%d N=%d kblocks=%d block_n=%d stages=%d bres=%d halo=%d mnB=%d grid=%d | CTA0 cycles %lld: "
+            "producer<-empty %lld, mma<-tmem_empty %lld, mma<-full %lld, epilogue<-tmem_full %lld\n",
+            p.M, p.N, p.num_k_blocks, p.block_n, p.stages, p.b_resident, p.halo, p.b_mn_major, grid, h[4], h[0], h[1],
+            h[2], h[3]);
+  }
   return 0;
 }
 
