@@ -63,6 +63,7 @@ struct GemmParams {
   int b_resident;
   // debug (B200_CONV_TRACE=1): CTA 0 accumulates the cycles its roles spend waiting on each barrier class
   long long* trace;
+  int ctas;               // 1, or 2: CTA pairs (cta_group::2) share 256-row tiles; set by plan_ctas() before map_b is built
 };
 
 constexpr int kHaloRows = 18, kHaloCols = 16;
@@ -111,13 +112,18 @@ __device__ long long g_trace[8];
     }                                                             \
   } while (0)
 
+// kCtas == 2: the CTAs of a cluster pair share one 256-row tile (cta_group::2): CTA r stages rows [128 r, +128) of A
+// and rows/columns [r * block_n / 2, +block_n / 2) of the B tile; the leader (rank 0) owns the full / tmem_empty
+// barriers and issues the MMAs, both CTAs drain their own 128 TMEM lanes.
+template <int kCtas>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_out, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int b_bytes = p.block_n * kBlockK * 2;
+  const int bn_cta = p.block_n / kCtas;          // B rows (K-major) or columns (MN-major) staged by this CTA
+  const int b_bytes = bn_cta * kBlockK * 2;
   // halo mode: [resident filter: 9 taps x b_bytes][stages x halo tile]; otherwise [stages x (A tile, B tile)]
   const int stage_bytes = p.halo ? kHaloBytes : (p.b_resident ? kABytes : kABytes + b_bytes);
   uint8_t* const bres = smem;
@@ -128,7 +134,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const uint32_t cr = kCtas == 2 ? cluster_ctarank() : 0u;
+  // tiles are (M tile group of kCtas x 128 rows, N tile); a cluster walks them with the stride of the cluster count
+  const int num_tiles = ((p.num_m_tiles + kCtas - 1) / kCtas) * p.num_n_tiles;
+  const int tile_first = blockIdx.x / kCtas, tile_step = gridDim.x / kCtas;
   const bool tr = p.trace != nullptr && blockIdx.x == 0;
   long long tr_acc[4] = {0, 0, 0, 0};
   const long long tr_start = tr ? clock64() : 0;
@@ -144,16 +153,26 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     for (int i = 0; i < kAccStages; ++i) {
       mbar_init(&bars->tmem_full[i], 1);
       // one arrive per epilogue warp that drains the stage: both groups of the pair when the tile has >= 2 boxes
-      mbar_init(&bars->tmem_empty[i], (p.tma_store && p.block_n >= 128) ? 8 : 4);
+      mbar_init(&bars->tmem_empty[i], ((p.tma_store && p.block_n >= 128) ? 8 : 4) * kCtas);
     }
     mbar_init(&bars->bres, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<kTmemCols>(&bars->tmem_base);
+  if (warp == 1) {
+    if constexpr (kCtas == 2) tmem_alloc_pair<kTmemCols>(&bars->tmem_base);
+    else tmem_alloc<kTmemCols>(&bars->tmem_base);
+  }
   tc_fence_before();
-  __syncthreads();
+  // the peer's barriers must be initialised before this CTA's TMA / commits / arrives can touch them
+  if constexpr (kCtas == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  // 2-D tiled load; in a pair the bytes are counted on the leader's barrier
+  auto load_2d = [](void* dst, const CUtensorMap* map, uint64_t* bar, int32_t c0, int32_t c1) {
+    if constexpr (kCtas == 2) tma_load_2d_pair(dst, map, bar, c0, c1);
+    else tma_load_2d(dst, map, bar, c0, c1);
+  };
 
   if (warp == 0) {
     // ================================================================ TMA producer
@@ -173,7 +192,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       const int per_img = p.tiles_x * p.tiles_y;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
         const int mt = tile / p.num_n_tiles;
         const int img = mt / per_img, rem = mt - img * per_img;
         const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
@@ -188,26 +207,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     } else if (lane == 0) {
       if (p.b_resident) {
         // gridDim.x is a multiple of num_n_tiles here, so this CTA only ever sees one N tile
-        const int n00 = (blockIdx.x % p.num_n_tiles) * p.block_n;
-        mbar_expect_tx(&bars->bres, (uint32_t)(p.num_k_blocks * b_bytes));
+        const int n00 = (tile_first % p.num_n_tiles) * p.block_n + (int)cr * bn_cta;
+        if (cr == 0) mbar_expect_tx(&bars->bres, (uint32_t)(p.num_k_blocks * b_bytes * kCtas));
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           const int tap = kb / p.cchunks, cc = kb - tap * p.cchunks;
           uint8_t* sb = bres + kb * b_bytes;
           if (!p.b_mn_major) {
-            tma_load_2d(sb, &map_b, &bars->bres, p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n00);
+            load_2d(sb, &map_b, &bars->bres, p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n00);
           } else {
             const int r = tap / p.S, s2 = tap - r * p.S;
             const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s2);
-            for (int j = 0; j < p.block_n / 64; ++j)
-              tma_load_2d(sb + j * (kBlockK * 128), &map_b, &bars->bres, wtap * p.b_row_len + n00 + j * 64, cc * kBlockK);
+            for (int j = 0; j < bn_cta / 64; ++j)
+              load_2d(sb + j * (kBlockK * 128), &map_b, &bars->bres, wtap * p.b_row_len + n00 + j * 64, cc * kBlockK);
           }
         }
       }
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
-        const int m0 = mt * kBlockM, n0 = nt * p.block_n;
+      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+        // an odd tile count leaves the last pair's second CTA without rows: it re-loads the last real tile (its
+        // accumulators are never stored) so the pair's byte count and MMA shape stay uniform
+        int mt = (tile / p.num_n_tiles) * kCtas + (int)cr;
+        if (mt >= p.num_m_tiles) mt = p.num_m_tiles - 1;
+        const int nt = tile % p.num_n_tiles;
+        const int m0 = mt * kBlockM, n0 = nt * p.block_n + (int)cr * bn_cta;
         int img = 0, ph = 0, qw = 0;
         if (p.a_im2col) {
           img = m0 / p.PQ;
@@ -220,26 +243,29 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           TRACED_WAIT(0, mbar_wait(&bars->empty[stage], phase ^ 1));
           uint8_t* sa = smem + (size_t)stage * stage_bytes;
           uint8_t* sb = sa + kABytes;
-          mbar_expect_tx(&bars->full[stage], (uint32_t)stage_bytes);
+          if (cr == 0) mbar_expect_tx(&bars->full[stage], (uint32_t)(stage_bytes * kCtas));
           const int tap = kb / p.cchunks, cc = kb - tap * p.cchunks;
           const int r = tap / p.S, s = tap - r * p.S;
           if (p.a_im2col) {
-            tma_load_im2col_4d(sa, &map_a, &bars->full[stage], cc * kBlockK, qw, ph, img, (uint16_t)s, (uint16_t)r);
+            if constexpr (kCtas == 2)
+              tma_load_im2col_4d_pair(sa, &map_a, &bars->full[stage], cc * kBlockK, qw, ph, img, (uint16_t)s, (uint16_t)r);
+            else
+              tma_load_im2col_4d(sa, &map_a, &bars->full[stage], cc * kBlockK, qw, ph, img, (uint16_t)s, (uint16_t)r);
           } else {
-            tma_load_2d(sa, &map_a, &bars->full[stage], kb * kBlockK, m0);
+            load_2d(sa, &map_a, &bars->full[stage], kb * kBlockK, m0);
           }
           if (p.b_resident) {
             // filter already in shared memory
           } else if (!p.b_mn_major) {
             // K-major weights [Cout][(r,s),Cin]: chunk cc of tap (r,s). With Cin % 64 != 0 the last chunk of a tap
             // runs into the next tap's channels; the matching A columns were zero-filled by TMA, so they add nothing.
-            tma_load_2d(sb, &map_b, &bars->full[stage], p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n0);
+            load_2d(sb, &map_b, &bars->full[stage], p.a_im2col ? tap * p.b_row_len + cc * kBlockK : kb * kBlockK, n0);
           } else {
             // weight row = one output channel (GEMM K index); columns = ((r,s), cin). Taps are flipped.
             const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s);
-            for (int j = 0; j < p.block_n / 64; ++j)
-              tma_load_2d(sb + j * (kBlockK * 128), &map_b, &bars->full[stage], wtap * p.b_row_len + n0 + j * 64,
-                          cc * kBlockK);
+            for (int j = 0; j < bn_cta / 64; ++j)
+              load_2d(sb + j * (kBlockK * 128), &map_b, &bars->full[stage], wtap * p.b_row_len + n0 + j * 64,
+                      cc * kBlockK);
           }
           if (++stage == p.stages) {
             stage = 0;
@@ -248,15 +274,23 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================================================ MMA issuer
-    const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
+  } else if (warp == 1 && cr == 0) {
+    // ================================================================ MMA issuer (the pair's leader only)
+    const uint32_t idesc = make_idesc_bf16(kBlockM * kCtas, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
+    auto mma = [](uint32_t d, uint64_t da, uint64_t db, uint32_t id, uint32_t accum) {
+      if constexpr (kCtas == 2) mma_bf16_pair(d, da, db, id, accum);
+      else mma_bf16(d, da, db, id, accum);
+    };
+    auto commit = [](uint64_t* bar) {
+      if constexpr (kCtas == 2) mma_commit_pair(bar);
+      else mma_commit(bar);
+    };
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     if (p.halo || p.b_resident) mbar_wait(&bars->bres, 0);
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
       TRACED_WAIT(1, mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1));
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN);
@@ -278,11 +312,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               const uint64_t da = make_sdesc_sw128(a0 + k * 32, 16, kHaloCols * 128);
               const uint64_t db = p.b_mn_major ? make_sdesc_sw128(b0 + k * 2048, kBlockK * 128, 1024)
                                                : make_sdesc_sw128(b0 + k * 32, 16, 1024);
-              mma_bf16(d_tmem, da, db, idesc, (tap | k) != 0 ? 1u : 0u);
+              mma(d_tmem, da, db, idesc, (tap | k) != 0 ? 1u : 0u);
             }
           }
-          mma_commit(&bars->empty[stage]);
-          mma_commit(&bars->tmem_full[acc]);
+          commit(&bars->empty[stage]);
+          commit(&bars->tmem_full[acc]);
         }
         __syncwarp();
         if (++stage == p.stages) {
@@ -301,10 +335,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint64_t da = make_sdesc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = p.b_mn_major ? make_sdesc_sw128(sb + k * 2048, kBlockK * 128, 1024)
                                              : make_sdesc_sw128(sb + k * 32, 16, 1024);
-            mma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            mma(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          mma_commit(&bars->empty[stage]);                       // frees the smem slot when the MMAs have read it
-          if (kb == p.num_k_blocks - 1) mma_commit(&bars->tmem_full[acc]);
+          commit(&bars->empty[stage]);                           // frees the smem slot (in both CTAs of a pair)
+          if (kb == p.num_k_blocks - 1) commit(&bars->tmem_full[acc]);
         }
         __syncwarp();
         if (++stage == p.stages) {
@@ -317,8 +351,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         acc_phase ^= 1;
       }
     }
-  } else {
+  } else if (warp >= 2) {
     // ================================================================ epilogue (warps 2..17 = groups 0..3)
+    // handing a drained accumulator stage back: the MMA issuer waits on the leader's barrier
+    auto release_acc = [&](uint64_t* bar) {
+      if (kCtas == 2 && cr != 0) mbar_arrive_cluster(bar, 0);
+      else mbar_arrive(bar);
+    };
     const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
     const int grp = (warp - 2) >> 2;            // 0..3
     const int acc = grp >> 1;                   // pair a = groups 2a, 2a+1 owns accumulator stage a: tiles a, a+2, ...
@@ -347,10 +386,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int bar_id = 1 + grp;
       bool store_pending = false;
       int tile_i = 0;
-      for (int tile = blockIdx.x; tile < num_tiles && bx0 < bx1; tile += gridDim.x, ++tile_i) {
+      for (int tile = tile_first; tile < num_tiles && bx0 < bx1; tile += tile_step, ++tile_i) {
         if ((tile_i & 1) != acc) continue;
-        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+        const int mt = (tile / p.num_n_tiles) * kCtas + (int)cr, nt = tile % p.num_n_tiles;
         const int n0 = nt * p.block_n;
+        if (kCtas == 2 && mt >= p.num_m_tiles) {
+          // rowless second half of the last pair: nothing to store, just hand the stage back
+          mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
+          tc_fence_after();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) release_acc(&bars->tmem_empty[acc]);
+          acc_phase ^= 1;
+          continue;
+        }
         int h_img = 0, h_y0 = 0, h_x0 = 0;           // halo mode: image and top-left output pixel of this tile
         if (p.halo) {
           const int per_img = p.tiles_x * p.tiles_y;
@@ -402,7 +451,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             // all of this tile's accumulators are out of TMEM: hand the stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+            if (lane == 0) release_acc(&bars->tmem_empty[acc]);
           }
           fence_proxy_async();
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
@@ -464,15 +513,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     } else {
       int tile_i = 0;
       // narrow / fp32 outputs: the first group of each pair drains the whole tile
-      for (int tile = blockIdx.x; tile < num_tiles && half == 0; tile += gridDim.x, ++tile_i) {
+      for (int tile = tile_first; tile < num_tiles && half == 0; tile += tile_step, ++tile_i) {
         if ((tile_i & 1) != acc) continue;
-        const int mt = tile / p.num_n_tiles, nt = tile % p.num_n_tiles;
+        const int mt = (tile / p.num_n_tiles) * kCtas + (int)cr, nt = tile % p.num_n_tiles;
         const int row = mt * kBlockM + lane_group * 32 + lane;
         const int n0 = nt * p.block_n;
         mbar_wait_backoff(&bars->tmem_full[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * kMaxBlockN);
-        const bool valid = row < p.M;
+        // the rowless second half of the last pair holds a copy of the last real tile: no stores, no statistics
+        const bool ghost = kCtas == 2 && mt >= p.num_m_tiles;
+        const bool valid = row < p.M && !ghost;
         size_t orow = (size_t)row;
         if (p.scatter && valid) {
           const int img = row / p.PQ;
@@ -484,7 +535,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           uint32_t r[16];
           tmem_ld_x16(t_row + (uint32_t)c, r);
           tmem_ld_wait();
-          if (p.col_stats) {
+          if (p.col_stats && !ghost) {
             // per-column sum / sum of squares over this warp's 32 rows (rows past M contribute zeros: their A rows
             // were zero-filled by TMA), via a halving butterfly: 16+8+4+2+1 shuffles per statistic
             float s1[16], s2[16];
@@ -552,7 +603,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+        if (lane == 0) release_acc(&bars->tmem_empty[acc]);
         acc_phase ^= 1;
       }
     }
@@ -574,7 +625,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 
   tc_fence_before();
-  __syncthreads();
+  // a pair leaves together: the peer may still read this CTA's operands or signal its barriers
+  if constexpr (kCtas == 2) cluster_sync_all();
+  else __syncthreads();
   if (tr && lane == 0) {
     // slots 0..2 have one writer each; slot 3 = epilogue warp 2 (group 0, lane group 2); slot 4 = CTA lifetime
     if (warp == 0) p.trace[0] = tr_acc[0];
@@ -587,7 +640,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<kTmemCols>(tmem_base);
+    if constexpr (kCtas == 2) tmem_dealloc_pair<kTmemCols>(tmem_base);
+    else tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
 
@@ -608,8 +662,52 @@ int pick_block_n(int n) {
   return (n + 15) / 16 * 16;   // narrow outputs: one tile, direct-store epilogue masks the tail
 }
 
+// CTA pairs need a tile width that splits into two 64-column-aligned halves and more than one M tile. They pay off
+// where the main loop is long (measured on ResNet-50 layers: >= 8 k-blocks; 5-13% for 256-wide tiles and for the
+// MN-major weight operand of dgrad); short-K memory-bound layers lose a little to the cross-CTA hand-offs per tile.
+int plan_ctas(int block_n, int num_m_tiles, int num_k_blocks, bool b_mn_major) {
+  static const int mode = getenv("B200_CONV_2CTA") ? atoi(getenv("B200_CONV_2CTA")) : 1;   // 0 off, 1 auto, 2 always
+  if (mode == 0 || block_n % 128 != 0 || num_m_tiles < 2 || num_k_blocks <= 0) return 1;
+  if (mode == 2) return 2;
+  return (num_k_blocks >= 8 && (block_n == 256 || b_mn_major)) ? 2 : 1;
+}
+
+// persistent grid: one CTA (or CTA pair) per SM (pair), never more than there are tiles
+int plan_grid(int num_m_tiles, int num_n_tiles, int ctas) {
+  const int groups = (num_m_tiles + ctas - 1) / ctas * num_n_tiles;
+  const int max_groups = kNumSMs / ctas;
+  return (groups < max_groups ? groups : max_groups) * ctas;
+}
+
+template <int kCtas>
+cudaError_t launch_kernel(int grid, size_t smem, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb,
+                          const CUtensorMap& mo, const GemmParams& p) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<kCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = kCtas > 1 ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, conv_gemm_kernel<kCtas>, ma, mb, mo, p);
+}
+
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStream_t st) {
-  const int stage_bytes = kABytes + p.block_n * kBlockK * 2;
+  if (p.ctas < 1) p.ctas = 1;
+  if (p.halo) p.ctas = 1;
+  const int bn_cta = p.block_n / p.ctas;
+  const int stage_bytes = kABytes + bn_cta * kBlockK * 2;
   // bf16 row-major outputs whose tile width is a multiple of 64 go out through shared memory + TMA bulk stores
   CUtensorMap mo;
   p.tma_store = (!p.out_fp32 && p.block_n % 64 == 0 && p.N % 8 == 0 && p.ldo % 8 == 0) ? 1 : 0;
@@ -631,8 +729,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
     // keep the filter slice resident when it is small and every CTA sticks to one N tile (memory-bound 1x1 layers:
     // the per-tile filter reload would otherwise be most of the L2 traffic)
     static const bool res_ok = !(getenv("B200_CONV_BRES") && getenv("B200_CONV_BRES")[0] == '0');
-    const int64_t bres_bytes = (int64_t)p.num_k_blocks * p.block_n * kBlockK * 2;
-    const int grid0 = tiles_all < kNumSMs ? tiles_all : kNumSMs;
+    const int64_t bres_bytes = (int64_t)p.num_k_blocks * bn_cta * kBlockK * 2;
+    const int grid0 = plan_grid(p.num_m_tiles, p.num_n_tiles, p.ctas) / p.ctas;
     static const int res_max_kb = getenv("B200_CONV_BRES_KB") ? atoi(getenv("B200_CONV_BRES_KB")) : 96;
     // at least two 16 KiB activation stages must still fit next to the resident slice
     const bool fits = fixed + bres_bytes + 2 * kABytes <= 227 * 1024;
@@ -648,13 +746,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
   if (stages < 2) stages = 2;
   p.stages = stages;
   const size_t smem = (size_t)stages * stage_bytes_eff + fixed;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
-  const int tiles = p.num_m_tiles * p.num_n_tiles;
-  int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  int grid = plan_grid(p.num_m_tiles, p.num_n_tiles, p.ctas);
   if (p.halo) grid = grid / p.num_n_tiles * p.num_n_tiles;   // a CTA keeps one N tile's filter resident
   static const bool trace_on = getenv("B200_CONV_TRACE") && getenv("B200_CONV_TRACE")[0] == '1';
   static long long* trace_buf = nullptr;
@@ -664,16 +756,17 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
     B200_CUDA(cudaMemsetAsync(trace_buf, 0, 8 * sizeof(long long), st));
     p.trace = trace_buf;
   }
-  conv_gemm_kernel<<<grid, kThreads, smem, st>>>(ma, mb, mo, p);
+  if (p.ctas == 2) B200_CUDA(launch_kernel<2>(grid, smem, st, ma, mb, mo, p));
+  else B200_CUDA(launch_kernel<1>(grid, smem, st, ma, mb, mo, p));
   B200_LAUNCH_CHECK();
   if (trace_on) {
     long long h[8];
     B200_CUDA(cudaStreamSynchronize(st));
     B200_CUDA(cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost));
     fprintf(stderr,
-            "[conv trace] M=%d N=%d kblocks=%d block_n=%d stages=%d bres=%d halo=%d mnB=%d grid=%d | CTA0 cycles %lld: "
+            "[conv trace] M=%d N=%d kblocks=%d block_n=%d stages=%d bres=%d halo=%d mnB=%d grid=%d ctas=%d | CTA0 cycles %lld: "
             "producer<-empty %lld, mma<-tmem_empty %lld, mma<-full %lld, epilogue<-tmem_full %lld\n",
-            p.M, p.N, p.num_k_blocks, p.block_n, p.stages, p.b_resident, p.halo, p.b_mn_major, grid, h[4], h[0], h[1],
+            p.M, p.N, p.num_k_blocks, p.block_n, p.stages, p.b_resident, p.halo, p.b_mn_major, grid, p.ctas, h[4], h[0], h[1],
             h[2], h[3]);
   }
   return 0;
@@ -768,9 +861,11 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   p.M = g->n * g->p * g->q;
   p.N = g->k;
   p.block_n = pick_block_n(g->k);
-  const int kdim = g->r * g->s * g->c;
-  if (tmap_tiled_2d(&mb, w, 2, (uint64_t)kdim, (uint64_t)g->k, (uint64_t)kdim * 2, kBlockK, p.block_n, true)) return -1;
   p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
+  p.ctas = plan_ctas(p.block_n, p.num_m_tiles, g->r * g->s * ((g->c + kBlockK - 1) / kBlockK), false);
+  const int kdim = g->r * g->s * g->c;
+  if (tmap_tiled_2d(&mb, w, 2, (uint64_t)kdim, (uint64_t)g->k, (uint64_t)kdim * 2, kBlockK, p.block_n / p.ctas, true))
+    return -1;
   p.num_n_tiles = (p.N + p.block_n - 1) / p.block_n;
   p.cchunks = (g->c + kBlockK - 1) / kBlockK;
   p.num_k_blocks = g->r * g->s * p.cchunks;
@@ -790,23 +885,25 @@ int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const 
   return launch(ma, mb, p, static_cast<cudaStream_t>(stream));
 }
 
-static int64_t grid_for_tiles(int64_t m, int n) {
+static int64_t grid_for_tiles(int64_t m, int n, int num_k_blocks) {
   const int bn = pick_block_n(n);
-  int64_t tiles = (m + kBlockM - 1) / kBlockM * ((n + bn - 1) / bn);
-  return tiles < kNumSMs ? tiles : kNumSMs;
+  const int mt = (int)((m + kBlockM - 1) / kBlockM), nt = (n + bn - 1) / bn;
+  return plan_grid(mt, nt, plan_ctas(bn, mt, num_k_blocks, false));
 }
+
+static int conv_k_blocks(const b200_conv_geom* g) { return g->r * g->s * ((g->c + kBlockK - 1) / kBlockK); }
 
 int64_t b200_conv_stats_rows(const b200_conv_geom* g) {
   // per CTA of the persistent grid: 8 scratch rows (epilogue group x 32-row group) + 1 folded row at the end
   if (!g) return -1;
   if (halo_shape(g, g->c, g->k)) return halo_grid(g, g->k) * 9;
-  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 9;
+  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k, conv_k_blocks(g)) * 9;
 }
 
 int64_t b200_conv_stats_first_result_row(const b200_conv_geom* g) {
   if (!g) return -1;
   if (halo_shape(g, g->c, g->k)) return halo_grid(g, g->k) * 8;
-  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k) * 8;
+  return grid_for_tiles((int64_t)g->n * g->p * g->q, g->k, conv_k_blocks(g)) * 8;
 }
 
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream) {
@@ -869,6 +966,7 @@ int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, cons
   const int row = g->r * g->s * g->c;
   if (tmap_tiled_2d(&mb, w, 2, (uint64_t)row, (uint64_t)g->k, (uint64_t)row * 2, 64, kBlockK, true)) return -1;
   p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;
+  p.ctas = plan_ctas(p.block_n, p.num_m_tiles, g->r * g->s * ((g->k + kBlockK - 1) / kBlockK), true);
   p.num_n_tiles = (p.N + p.block_n - 1) / p.block_n;
   p.cchunks = (g->k + kBlockK - 1) / kBlockK;
   p.num_k_blocks = g->r * g->s * p.cchunks;
@@ -896,6 +994,7 @@ int b200_gemm_nn(const b200_bf16* a, int32_t lda, const b200_bf16* b, b200_bf16*
   if (tmap_tiled_2d(&ma, a, 2, (uint64_t)lda, (uint64_t)m, (uint64_t)lda * 2, kBlockK, kBlockM, true)) return -1;
   if (tmap_tiled_2d(&mb, b, 2, (uint64_t)n, (uint64_t)k, (uint64_t)n * 2, 64, kBlockK, true)) return -1;
   p.num_m_tiles = (m + kBlockM - 1) / kBlockM;
+  p.ctas = plan_ctas(p.block_n, p.num_m_tiles, (k + kBlockK - 1) / kBlockK, true);
   p.num_n_tiles = n / p.block_n;
   p.cchunks = (k + kBlockK - 1) / kBlockK;
   p.num_k_blocks = p.cchunks;
@@ -915,8 +1014,9 @@ int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, i
   return b200_gemm_nt_stats(a, b, out, m, n, k, ldo, out_fp32, nullptr, stream);
 }
 
-int64_t b200_gemm_stats_rows(int32_t m, int32_t n) { return grid_for_tiles(m, n) * 9; }
-int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n) { return grid_for_tiles(m, n) * 8; }
+// (the scratch rows of the GEMM-with-statistics call are sized from (m, n) alone, so that call keeps one CTA per tile)
+int64_t b200_gemm_stats_rows(int32_t m, int32_t n) { return grid_for_tiles(m, n, 0) * 9; }
+int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n) { return grid_for_tiles(m, n, 0) * 8; }
 
 int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
                        int32_t ldo, int32_t out_fp32, float* col_stats, void* stream) {
@@ -927,9 +1027,10 @@ int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_
   p.M = m;
   p.N = n;
   p.block_n = pick_block_n(n);
-  if (tmap_tiled_2d(&ma, a, 2, (uint64_t)k, (uint64_t)m, (uint64_t)k * 2, kBlockK, kBlockM, true)) return -1;
-  if (tmap_tiled_2d(&mb, b, 2, (uint64_t)k, (uint64_t)n, (uint64_t)k * 2, kBlockK, p.block_n, true)) return -1;
   p.num_m_tiles = (m + kBlockM - 1) / kBlockM;
+  p.ctas = col_stats ? 1 : plan_ctas(p.block_n, p.num_m_tiles, k / kBlockK, false);
+  if (tmap_tiled_2d(&ma, a, 2, (uint64_t)k, (uint64_t)m, (uint64_t)k * 2, kBlockK, kBlockM, true)) return -1;
+  if (tmap_tiled_2d(&mb, b, 2, (uint64_t)k, (uint64_t)n, (uint64_t)k * 2, kBlockK, p.block_n / p.ctas, true)) return -1;
   p.num_n_tiles = (n + p.block_n - 1) / p.block_n;
   p.cchunks = k / kBlockK;
   p.num_k_blocks = p.cchunks;

@@ -57,6 +57,9 @@ CASES = [
     (2, 17, 17, 128, 192, (7, 1), 1, ((3, 3), (0, 0))),
     (2, 35, 35, 64, 96, 3, 1, ((1, 1), (1, 1))),
     (2, 224, 224, 64, 64, 3, 1, ((1, 1), (1, 1))),      # VGG conv1_2
+    # CTA-pair (cta_group::2) mode with an odd number of 128-row tiles: the last pair's second CTA has no rows
+    (3, 14, 14, 512, 256, 1, 1, ((0, 0), (0, 0))),      # fprop in pair mode (8 k-blocks, 256-wide tile), 5 M tiles
+    (3, 14, 14, 256, 512, 1, 1, ((0, 0), (0, 0))),      # dgrad in pair mode, 5 M tiles
 ]
 
 
