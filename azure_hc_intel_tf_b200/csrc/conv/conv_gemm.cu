@@ -563,7 +563,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               }
             }
             // lane l now holds column (l & 15) of this chunk (both 16-lane halves hold the same totals)
-            if (lane < 16) {
+            if (lane < 16 && n0 + c + lane < p.N) {
               const int col = lane;
               float* dst = p.col_stats + (((size_t)blockIdx.x * 2 + acc) * 4 + lane_group) * 2 * p.N + n0 + c + col;
               dst[0] += s1[0];
@@ -804,6 +804,16 @@ static int64_t halo_grid(const b200_conv_geom* g, int out_ch) {
 
 extern "C" int b200_conv_wgrad_supported(const b200_conv_geom* g);
 
+// smallest INPUT channel count the TMA paths take. A 64-channel box over fewer channels is zero-filled past the edge,
+// so thinner layers compute correctly (B200_CONV_MIN_C=8 enables them), but half of every k-block / output tile is
+// then idle and the library measured ~2x faster on those layers (Inception-v3 32x149x149, GoogLeNet 5x5 branches),
+// so the default keeps Cin >= 64 here. A thin OUTPUT side (1x1 reductions to 16..48 channels) is always taken.
+extern "C" int b200_conv_min_channels() {
+  static const int v = getenv("B200_CONV_MIN_C") ? atoi(getenv("B200_CONV_MIN_C")) : 64;
+  return v;
+}
+static int min_channels() { return b200_conv_min_channels(); }
+
 extern "C" {
 
 int b200_conv_supported(const b200_conv_geom* g, int op) {
@@ -812,10 +822,12 @@ int b200_conv_supported(const b200_conv_geom* g, int op) {
   if (op == B200_CONV_WGRAD) return b200_conv_wgrad_supported(g);
   if (op == B200_CONV_FPROP) {
     // channel chunks past Cin are zero-filled by TMA, so Cin only has to keep rows 16-byte aligned
-    return g->c >= 64 && g->c % 8 == 0 && g->k % 16 == 0 && g->r <= 15 && g->s <= 15;
+    return g->c >= min_channels() && g->c % 8 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15;
   }
   if (op == B200_CONV_DGRAD) {
-    if (g->k < 64 || g->c < 64 || g->k % 8 != 0 || g->c % 8 != 0) return 0;
+    // the reduction runs over Cout here, so a thin Cout only leaves part of a 64-channel k-block idle; a thin Cin
+    // would be a thin output tile, which the library handles better
+    if (g->c < min_channels() || g->k % 8 != 0 || g->c % 8 != 0) return 0;
     if (g->stride_h == 1 && g->stride_w == 1) return g->r <= 15 && g->s <= 15;
     // strided: only 1x1 without padding (ResNet v1 down-sampling convolutions)
     return g->r == 1 && g->s == 1 && g->pad_t == 0 && g->pad_l == 0 && g->pad_b == 0 && g->pad_r == 0 &&
@@ -827,7 +839,7 @@ int b200_conv_supported(const b200_conv_geom* g, int op) {
 int b200_conv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, float* col_stats,
                     void* stream) {
   B200_CHECK_ARG(x && w && y && g, "conv_fprop: null pointer");
-  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin>=64, Cin%%8==0, Cout%%16==0)");
+  B200_CHECK_ARG(b200_conv_supported(g, B200_CONV_FPROP), "conv_fprop: unsupported geometry (need Cin>=64, Cin%%8==0, Cout%%8==0)");
   CUtensorMap ma, mb;
   if (halo_shape(g, g->c, g->k)) {
     GemmParams p{};
@@ -962,7 +974,7 @@ int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, cons
   p.N = g->c;
   // tile width: a multiple of 64 (the MN-major weight boxes are 64 columns wide); columns past Cin are zero-filled on
   // load and clipped on store
-  p.block_n = g->c % 256 == 0 ? 256 : (g->c % 128 == 0 ? 128 : (g->c % 64 == 0 ? 64 : (g->c > 192 ? 256 : (g->c > 128 ? 192 : 128))));
+  p.block_n = g->c % 256 == 0 ? 256 : (g->c % 128 == 0 ? 128 : (g->c % 64 == 0 ? 64 : (g->c > 192 ? 256 : (g->c > 128 ? 192 : (g->c > 64 ? 128 : 64)))));
   const int row = g->r * g->s * g->c;
   if (tmap_tiled_2d(&mb, w, 2, (uint64_t)row, (uint64_t)g->k, (uint64_t)row * 2, 64, kBlockK, true)) return -1;
   p.num_m_tiles = (p.M + kBlockM - 1) / kBlockM;

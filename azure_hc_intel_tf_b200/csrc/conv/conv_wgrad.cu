@@ -420,13 +420,15 @@ using namespace b200;
 
 extern "C" {
 
+int b200_conv_min_channels();
+
 int b200_conv_wgrad_supported(const b200_conv_geom* g) {
   if (!g) return 0;
-  return g->c >= 64 && g->c % 8 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0;
+  return g->c >= b200_conv_min_channels() && g->c % 8 == 0 && g->k % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0;
 }
 
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g) {
-  if (!g || g->c < 64 || g->c % 8 != 0) return 0;
+  if (!g || g->c < b200_conv_min_channels() || g->c % 8 != 0) return 0;
   WgradParams p{};
   plan(g, p);
   return p.slices > 1 ? (int64_t)p.slices * p.out_elems * 4 : 0;
@@ -468,8 +470,8 @@ int b200_dense_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, int32_t
 static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, int dy_ld,
                       void* workspace, void* stream) {
   B200_CHECK_ARG(x && dy && dw && g, "conv_wgrad: null pointer");
-  B200_CHECK_ARG(g->c >= 64 && g->c % 8 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
-                 "conv_wgrad: unsupported geometry (need Cin>=64, Cin%%8==0, dy row stride %%8==0)");
+  B200_CHECK_ARG(g->c >= b200_conv_min_channels() && g->c % 8 == 0 && dy_ld % 8 == 0 && g->r <= 15 && g->s <= 15 && g->n > 0,
+                 "conv_wgrad: unsupported geometry (need Cin%%8==0, dy row stride %%8==0)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   WgradParams p{};
   plan(g, p);
