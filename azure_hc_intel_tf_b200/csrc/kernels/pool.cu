@@ -56,6 +56,59 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const b200_bf16* __res
   }
 }
 
+// Forward with a compile-time window: all KH*KW vector loads of an output are issued before the first compare, so a
+// thread has the whole window in flight instead of one load per loop trip (ResNet 3x3/2: 0.23 ms with the loop).
+template <int KH, int KW>
+__global__ void __launch_bounds__(256) maxpool_fwd_fixed_kernel(const b200_bf16* __restrict__ x, b200_bf16* __restrict__ y,
+                                                                uint8_t* __restrict__ idx, b200_pool_geom g) {
+  const int cv = g.c / 8;
+  const uint32_t total = (uint32_t)g.n * g.p * g.q * cv;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cv);
+    uint32_t t = i / cv;
+    const int q = (int)(t % g.q);
+    t /= g.q;
+    const int p = (int)(t % g.p);
+    const int n = (int)(t / g.p);
+    const int h0 = p * g.sh - g.pad_t, w0 = q * g.sw - g.pad_l;
+    bf16x8 v[KH * KW];
+    bool ok[KH * KW];
+#pragma unroll
+    for (int r = 0; r < KH; ++r)
+#pragma unroll
+      for (int s = 0; s < KW; ++s) {
+        const int h = h0 + r, w = w0 + s;
+        ok[r * KW + s] = h >= 0 && h < g.h && w >= 0 && w < g.w;
+        if (ok[r * KW + s]) v[r * KW + s] = ld8(x + (((int64_t)n * g.h + h) * g.w + w) * g.c + c8 * 8);
+      }
+    float best[8];
+    int arg[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      best[k] = -INFINITY;
+      arg[k] = 0;
+    }
+#pragma unroll
+    for (int j = 0; j < KH * KW; ++j) {
+      if (!ok[j]) continue;
+      float f[8];
+      unpack8(v[j], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (f[k] > best[k]) {
+          best[k] = f[k];
+          arg[k] = j;
+        }
+      }
+    }
+    st8(y + (int64_t)i * 8, pack8(best));
+    uint2 pk;
+    pk.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+    pk.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    *reinterpret_cast<uint2*>(idx + (int64_t)i * 8) = pk;
+  }
+}
+
 template <typename Idx>
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const b200_bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
                                                           b200_bf16* __restrict__ dx, b200_pool_geom g) {
@@ -99,6 +152,73 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const b200_bf16* __res
       }
     }
     st8(dx + (int64_t)i * 8, pack8(acc));
+  }
+}
+
+// Backward of max pooling for stride SH x SW (compile-time): one thread owns an SH x SW block of input pixels (8
+// channels) and visits every output whose window can touch the block once, routing each channel's gradient to the
+// input position its saved argmax names. Against the one-input-pixel-per-thread kernel above this reads each
+// (dy, argmax) pair SH*SW times less often (ResNet's 3x3/2 pool: 0.49 ms -> L2 traffic cut 4x).
+template <int SH, int SW>
+__global__ void __launch_bounds__(256) maxpool_bwd_block_kernel(const b200_bf16* __restrict__ dy,
+                                                                const uint8_t* __restrict__ idx,
+                                                                b200_bf16* __restrict__ dx, b200_pool_geom g) {
+  const int cv = g.c / 8;
+  const int hb = (g.h + SH - 1) / SH, wb = (g.w + SW - 1) / SW;
+  const uint32_t total = (uint32_t)g.n * hb * wb * cv;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cv);
+    uint32_t t = i / cv;
+    const int bw = (int)(t % wb);
+    t /= wb;
+    const int bh = (int)(t % hb);
+    const int n = (int)(t / hb);
+    const int h0 = bh * SH, w0 = bw * SW;
+    const int kw_recip = (65536 + g.kw - 1) / g.kw;
+    float acc[SH][SW][8];
+#pragma unroll
+    for (int a = 0; a < SH; ++a)
+#pragma unroll
+      for (int b = 0; b < SW; ++b)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[a][b][k] = 0.0f;
+    // outputs p with p*SH - pad_t <= h0 + SH - 1 and p*SH - pad_t + kh - 1 >= h0
+    int p_lo = (h0 + g.pad_t - g.kh + SH) / SH;
+    if (h0 + g.pad_t - g.kh + 1 <= 0) p_lo = 0;
+    int p_hi = (h0 + SH - 1 + g.pad_t) / SH;
+    if (p_hi > g.p - 1) p_hi = g.p - 1;
+    int q_lo = (w0 + g.pad_l - g.kw + SW) / SW;
+    if (w0 + g.pad_l - g.kw + 1 <= 0) q_lo = 0;
+    int q_hi = (w0 + SW - 1 + g.pad_l) / SW;
+    if (q_hi > g.q - 1) q_hi = g.q - 1;
+    for (int p = p_lo; p <= p_hi; ++p) {
+      const int dh0 = p * SH - g.pad_t - h0;           // block-relative row of the window's first tap
+      for (int q = q_lo; q <= q_hi; ++q) {
+        const int dw0 = q * SW - g.pad_l - w0;
+        const int64_t o = ((((int64_t)n * g.p + p) * g.q + q) * cv + c8) * 8;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+        float f[8];
+        unpack8(ld8(dy + o), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int a = ((k < 4 ? pk.x : pk.y) >> (8 * (k & 3))) & 0xff;
+          const int r = (a * kw_recip) >> 16, s2 = a - r * g.kw;     // a / kw, exact for a < 256
+          const int dh = dh0 + r, dw = dw0 + s2;
+#pragma unroll
+          for (int aa = 0; aa < SH; ++aa)
+#pragma unroll
+            for (int bb = 0; bb < SW; ++bb)
+              if (dh == aa && dw == bb) acc[aa][bb][k] += f[k];
+        }
+      }
+    }
+#pragma unroll
+    for (int aa = 0; aa < SH; ++aa)
+#pragma unroll
+      for (int bb = 0; bb < SW; ++bb) {
+        const int h = h0 + aa, w = w0 + bb;
+        if (h < g.h && w < g.w) st8(dx + ((((int64_t)n * g.h + h) * g.w + w) * cv + c8) * 8, pack8(acc[aa][bb]));
+      }
   }
 }
 
@@ -253,6 +373,17 @@ int b200_maxpool_fwd(const b200_bf16* x, b200_bf16* y, uint8_t* idx, const b200_
   if (int e = check_geom(g, "maxpool_fwd")) return e;
   B200_CHECK_ARG(x && y && idx, "maxpool_fwd: null pointer");
   int64_t total = (int64_t)g->n * g->p * g->q * (g->c / 8);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (total < (1ll << 31) && g->kh == 3 && g->kw == 3) {
+    maxpool_fwd_fixed_kernel<3, 3><<<grid_for(total, 256), 256, 0, st>>>(x, y, idx, *g);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
+  if (total < (1ll << 31) && g->kh == 2 && g->kw == 2) {
+    maxpool_fwd_fixed_kernel<2, 2><<<grid_for(total, 256), 256, 0, st>>>(x, y, idx, *g);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   if (total < (1ll << 31))
     maxpool_fwd_kernel<uint32_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, idx, *g);
   else
@@ -265,6 +396,12 @@ int b200_maxpool_bwd(const b200_bf16* dy, const uint8_t* idx, b200_bf16* dx, con
   if (int e = check_geom(g, "maxpool_bwd")) return e;
   B200_CHECK_ARG(dy && dx && idx, "maxpool_bwd: null pointer");
   int64_t total = (int64_t)g->n * g->h * g->w * (g->c / 8);
+  if (g->sh == 2 && g->sw == 2 && total < (1ll << 31) && g->kh * g->kw <= 255) {
+    const int64_t blocks = (int64_t)g->n * ((g->h + 1) / 2) * ((g->w + 1) / 2) * (g->c / 8);
+    maxpool_bwd_block_kernel<2, 2><<<grid_for(blocks, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, idx, dx, *g);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   if (total < (1ll << 31))
     maxpool_bwd_kernel<uint32_t><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, idx, dx, *g);
   else

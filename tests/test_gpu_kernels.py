@@ -96,6 +96,7 @@ class _PoolM:
     ("max", (3, 3), (2, 2), ((0, 1), (0, 1)), (112, 112)),      # ResNet 'SAME' 112 -> 56
     ("max", (2, 2), (2, 2), ((0, 0), (0, 0)), (56, 56)),        # VGG
     ("max", (3, 3), (2, 2), ((0, 0), (0, 0)), (35, 35)),        # Inception 'VALID'
+    ("max", (3, 3), (2, 2), ((1, 1), (1, 1)), (27, 27)),        # odd size, padding on both sides
     ("max", (3, 3), (1, 1), ((1, 1), (1, 1)), (8, 8)),          # Inception-E / GoogLeNet 'SAME' stride 1
     ("avg", (3, 3), (1, 1), ((1, 1), (1, 1)), (17, 17)),        # Inception 'SAME' average
     ("avg", (8, 8), (1, 1), ((0, 0), (0, 0)), (8, 8)),
