@@ -40,6 +40,7 @@ SIGS = {
     "b200_softmax_xent": (i32, [vp, i32, vp, i32, i32, vp, vp, vp, i32, f32, vp]),
     "b200_normalize_u8": (i32, [vp, vp, i64, i32, i32, vp]),
     "b200_add": (i32, [vp, vp, vp, i64, vp]),
+    "b200_add_masked": (i32, [vp, vp, vp, vp, i64, vp]),
     "b200_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
 }
 

@@ -493,6 +493,25 @@ __global__ void __launch_bounds__(256) add_kernel(const b200_bf16* __restrict__ 
   }
 }
 
+// o = a + (mask bit ? b : 0): the gradient reaching a residual block's input is the main-path gradient plus the
+// block-output gradient gated by the output ReLU, whose mask bn_apply saved as one bit per element (one byte per
+// 8-channel vector). Doing the gate here means the gated copy is never written to memory.
+__global__ void __launch_bounds__(256) add_masked_kernel(const b200_bf16* __restrict__ a, const b200_bf16* __restrict__ b,
+                                                         const uint8_t* __restrict__ mask, b200_bf16* __restrict__ o,
+                                                         int64_t nvec) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < nvec; i += stride) {
+    float x[8], y[8];
+    unpack8(ld8_stream(a + i * 8), x);
+    unpack8(ld8_stream(b + i * 8), y);
+    const unsigned mb = __ldg(mask + i);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] += (mb >> k) & 1u ? y[k] : 0.0f;
+    st8(o + i * 8, pack8(x));
+  }
+}
+
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, b200_bf16* __restrict__ y, int64_t n) {
   int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
@@ -604,6 +623,14 @@ int b200_bias_act_bwd(const b200_bf16* dz, const b200_bf16* z, b200_bf16* dx, fl
 int b200_add(const b200_bf16* a, const b200_bf16* b, b200_bf16* out, int64_t n, void* stream) {
   B200_CHECK_ARG(a && b && out && n % 8 == 0, "add: need n%%8==0");
   add_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, out, n / 8);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_add_masked(const b200_bf16* a, const b200_bf16* b, const uint8_t* mask, b200_bf16* out, int64_t n,
+                    void* stream) {
+  B200_CHECK_ARG(a && b && mask && out && n % 8 == 0, "add_masked: need n%%8==0");
+  add_masked_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, mask, out, n / 8);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -35,9 +35,7 @@ class Bottleneck(nn.Module):
         b.pop_scope()
 
     def forward(self, x):
-        sc = x if self.shortcut is None else self.shortcut(x)
-        y = self.conv2(self.conv1(x))
-        return ops.conv_bn_add_relu(y, self.conv3, sc)
+        return ops.bottleneck(x, self)
 
 
 class ResNet(Model):

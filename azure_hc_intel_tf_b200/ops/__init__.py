@@ -67,6 +67,22 @@ def conv_bn_add_relu(x, m, residual):
     return batch_norm(y, m.bn, relu=True, residual=residual)
 
 
+def bottleneck(x, blk):
+    """ResNet bottleneck block: relu(bn3(conv3(relu(bn2(conv2(relu(bn1(conv1(x)))))))) + shortcut(x)). On the b200
+    kernels the block is one autograd node (ops/b200.py ``_Bottleneck``) so the gradient sum at the block input is
+    fused with the output ReLU's gate; B200_FUSED_BLOCK=0 falls back to chaining the per-layer nodes."""
+    if blk.cfg.kernels == "b200" and _fused_block() and _b200().bottleneck_supported(blk):
+        return _b200().bottleneck(x, blk)
+    sc = x if blk.shortcut is None else blk.shortcut(x)
+    y = blk.conv2(blk.conv1(x))
+    return conv_bn_add_relu(y, blk.conv3, sc)
+
+
+def _fused_block() -> bool:
+    import os
+    return os.environ.get("B200_FUSED_BLOCK", "1") != "0"
+
+
 # ------------------------------------------------------------------------------------ dense / pool
 
 def affine(x, m, relu: bool):

@@ -147,74 +147,177 @@ def bn_backward(dz, y, z_for_mask, stats, relu, want_dres, dgamma_out, dbeta_out
 
 # ------------------------------------------------------------------------------------ conv block
 
+def _cb_forward(x, weight, m, relu, residual):
+    """conv (+BN (+residual) (+ReLU) | +bias (+ReLU)) forward. Returns (z, saved) where ``saved`` is what
+    ``_cb_backward`` needs: (x or the first layer's patch matrix, bf16 weight, y, mask-or-z, stats, first)."""
+    x = nhwc(x)
+    if residual is not None:
+        residual = nhwc(residual)
+    w_lp = lowp(weight)
+    first = conv_impl.first_layer(x, m)       # Cin = 3: explicit patch matrix, kept for the weight gradient
+    if first:
+        y, sums, patches = conv_impl.first_fprop(x, w_lp, m, m.bn is not None and m.bn.training)
+        x = patches
+    if m.bn is not None:
+        if not first:
+            y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
+        z, stats, mask = bn_forward(y, m.bn, residual, relu, sums, want_mask=True)
+        # the ReLU mask is recomputed from y when there is no residual, else kept as one bit per element
+        return z, (x, w_lp, y, mask, stats, first)
+    if not first:
+        y = conv_impl.fprop(x, w_lp, m)
+    if m.bias is not None or relu:
+        n, c, h, w = y.shape
+        _check(lib().b200_bias_act(_ptr(y), _ptr(m.bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
+    return y, (x, w_lp, None, y if relu else None, None, first)
+
+
+def _cb_backward(saved, dz, m, relu, weight, gamma, beta, bias, need_dx, want_dres, gate=None):
+    """Backward of ``_cb_forward``. ``gate``: ReLU bit mask of a LATER layer that ``dz`` has not passed yet (the
+    projection shortcut of a residual block receives the block-output gradient before its ReLU gate); only for
+    BN layers without their own ReLU. Returns (dx, dres, gw, ggamma, gbeta, gbias) with the parameter entries
+    already run through ``_deliver`` (None when written into the fusion buffer)."""
+    x, w_lp, y, z, stats, first = saved
+    dz = nhwc(dz)
+    dres = dgamma = dbeta = dbias = None
+    g_gamma = g_beta = g_bias = None
+    if m.bn is not None:
+        g_gamma = _direct(gamma) if (gamma is not None and gamma.requires_grad) else None
+        g_beta = _direct(beta)
+        if gate is not None:
+            assert not relu, "a gated gradient can only enter a layer without its own ReLU"
+            dy, dres, dgamma, dbeta = bn_backward(dz, y, None, stats, True, want_dres, g_gamma, g_beta, mask=gate)
+        else:
+            dy, dres, dgamma, dbeta = bn_backward(dz, y, None, stats, relu, want_dres, g_gamma, g_beta, mask=z)
+    else:
+        assert gate is None
+        n, c, h, w = dz.shape
+        if bias is not None:
+            g_bias = _direct(bias)
+            dbias = g_bias if g_bias is not None else torch.empty(c, dtype=torch.float32, device=dz.device)
+            dy = empty_nhwc(n, c, h, w, dz.device) if relu else dz
+            _check(lib().b200_bias_act_bwd(_ptr(dz), _ptr(z), _ptr(dy) if relu else _ptr(None), _ptr(dbias),
+                                           n * h * w, c, int(relu), _ptr(scratch(dz.device)), _stream()),
+                   "bias_act_bwd")
+        elif relu:
+            dy = torch.where(z > 0, dz, torch.zeros_like(dz))
+        else:
+            dy = dz
+    g_w = _direct(weight)
+    if first:
+        dw = conv_impl.first_wgrad(x, dy, m, out=g_w)      # x holds the saved patch matrix
+        dx = None
+    else:
+        dw = conv_impl.wgrad(x, dy, m, out=g_w)
+        dx = conv_impl.dgrad(dy, w_lp, m, x.shape) if need_dx else None
+    return (dx, dres, _deliver(weight, g_w, dw),
+            _deliver(gamma, g_gamma, dgamma) if (gamma is not None and gamma.requires_grad) else None,
+            _deliver(beta, g_beta, dbeta) if beta is not None else None,
+            _deliver(bias, g_bias, dbias) if bias is not None else None)
+
+
 class _ConvBlock(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, gamma, beta, bias, residual, m, relu):
-        x = nhwc(x)
-        if residual is not None:
-            residual = nhwc(residual)
-        w_lp = lowp(weight)
-        ctx.m, ctx.relu = m, relu
-        ctx.has_res = residual is not None
-        first = conv_impl.first_layer(x, m)       # Cin = 3: explicit patch matrix, kept for the weight gradient
-        ctx.first = first
-        if first:
-            y, sums, patches = conv_impl.first_fprop(x, w_lp, m, m.bn is not None and m.bn.training)
-            x = patches
-        if m.bn is not None:
-            if not first:
-                y, sums = conv_impl.fprop(x, w_lp, m, want_stats=m.bn.training)
-            z, stats, mask = bn_forward(y, m.bn, residual, relu, sums, want_mask=True)
-            # the ReLU mask is recomputed from y when there is no residual, else kept as one bit per element
-            ctx.save_for_backward(x, w_lp, y, mask, stats)
-        else:
-            if not first:
-                y = conv_impl.fprop(x, w_lp, m)
-            if bias is not None or relu:
-                n, c, h, w = y.shape
-                _check(lib().b200_bias_act(_ptr(y), _ptr(bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
-            z = y
-            ctx.save_for_backward(x, w_lp, None, z if relu else None, None)
+        z, saved = _cb_forward(x, weight, m, relu, residual)
+        ctx.m, ctx.relu, ctx.has_res, ctx.first = m, relu, residual is not None, saved[5]
+        ctx.save_for_backward(*saved[:5])
         ctx.weight, ctx.gamma, ctx.beta, ctx.bias = weight, gamma, beta, bias
         return z
 
     @staticmethod
     def backward(ctx, dz):
-        m, relu = ctx.m, ctx.relu
-        x, w_lp, y, z, stats = ctx.saved_tensors
-        weight, gamma, beta, bias = ctx.weight, ctx.gamma, ctx.beta, ctx.bias
+        saved = tuple(ctx.saved_tensors) + (ctx.first,)
+        dx, dres, gw, gg, gb, gbias = _cb_backward(saved, dz, ctx.m, ctx.relu, ctx.weight, ctx.gamma, ctx.beta, ctx.bias,
+                                                   ctx.needs_input_grad[0], ctx.has_res)
+        return dx, gw, gg, gb, gbias, dres, None, None
+
+
+class _Bottleneck(torch.autograd.Function):
+    """A whole ResNet bottleneck block (conv1-bn-relu, conv2-bn-relu, conv3-bn, [projection conv-bn], add, relu) as
+    ONE autograd node. What that buys over chaining ``_ConvBlock`` nodes: the two gradient branches that meet at the
+    block input are summed here with one kernel that also applies the output ReLU's gate to the shortcut branch
+    (``b200_add_masked``), so the gated copy of the block-output gradient is never written (one activation-sized
+    write less per block) and autograd's own accumulation add disappears from the step.
+
+    Inputs: x, then (weight, gamma, beta) of conv1, conv2, conv3 and - for a projection shortcut - of the
+    shortcut conv. The reference runs this block as separate TF ops fused by MKL-DNN where it can
+    (tf_cnn_benchmarks resnet_model bottleneck_block, selected by run-tf-sing-ucx-openmpi.sh:34)."""
+
+    @staticmethod
+    def forward(ctx, x, blk, *params):
+        convs = [blk.conv1, blk.conv2, blk.conv3] + ([blk.shortcut] if blk.shortcut is not None else [])
+        ctx.blk, ctx.params, ctx.nconv = blk, params, len(convs)
+        x = nhwc(x)
+        tensors, firsts = [], []
+        sc = x
+        if blk.shortcut is not None:
+            sc, sv = _cb_forward(x, params[9], blk.shortcut, False, None)
+            tensors += sv[:5]
+            firsts.append(sv[5])
+        h = x
+        saved3 = []
+        for i, m in enumerate(convs[:3]):
+            h, sv = _cb_forward(h, params[3 * i], m, True, sc if i == 2 else None)
+            saved3.append(sv)
+        for sv in saved3:
+            tensors += sv[:5]
+        ctx.save_for_backward(*tensors)
+        return h
+
+    @staticmethod
+    def backward(ctx, dz):
+        blk, params = ctx.blk, ctx.params
+        t = list(ctx.saved_tensors)
+        proj = blk.shortcut is not None
+        off = 5 if proj else 0
+        sv = [tuple(t[off + 5 * i: off + 5 * i + 5]) + (False,) for i in range(3)]
         dz = nhwc(dz)
-        dres = dgamma = dbeta = dbias = None
-        g_gamma = g_beta = g_bias = None
-        if m.bn is not None:
-            g_gamma = _direct(gamma) if (gamma is not None and gamma.requires_grad) else None
-            g_beta = _direct(beta)
-            dy, dres, dgamma, dbeta = bn_backward(dz, y, None, stats, relu, ctx.has_res, g_gamma, g_beta, mask=z)
-        else:
-            n, c, h, w = dz.shape
-            if bias is not None:
-                g_bias = _direct(bias)
-                dbias = g_bias if g_bias is not None else torch.empty(c, dtype=torch.float32, device=dz.device)
-                dy = empty_nhwc(n, c, h, w, dz.device) if relu else dz
-                _check(lib().b200_bias_act_bwd(_ptr(dz), _ptr(z), _ptr(dy) if relu else _ptr(None), _ptr(dbias),
-                                               n * h * w, c, int(relu), _ptr(scratch(dz.device)), _stream()),
-                       "bias_act_bwd")
-            elif relu:
-                dy = torch.where(z > 0, dz, torch.zeros_like(dz))
+        grads = [None] * len(params)
+        # main path, last conv first; conv3's residual gradient stays implicit as (dz, its ReLU mask)
+        g = dz
+        for i in (2, 1, 0):
+            m = (blk.conv1, blk.conv2, blk.conv3)[i]
+            g, _, gw, gg, gb, _ = _cb_backward(sv[i], g, m, True, params[3 * i], params[3 * i + 1], params[3 * i + 2],
+                                              None, True, False)
+            grads[3 * i: 3 * i + 3] = [gw, gg, gb]
+        mask3 = sv[2][3]
+        n, c, hh, ww = (g.shape if g is not None else (0, 0, 0, 0))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = empty_nhwc(n, c, hh, ww, g.device)
+            if proj:
+                svp = tuple(t[0:5]) + (False,)
+                gp, _, gw, gg, gb, _ = _cb_backward(svp, dz, blk.shortcut, False, params[9], params[10], params[11], None,
+                                                    True, False, gate=mask3)
+                grads[9:12] = [gw, gg, gb]
+                _check(lib().b200_add(_ptr(g), _ptr(gp), _ptr(dx), g.numel(), _stream()), "add")
             else:
-                dy = dz
-        g_w = _direct(weight)
-        if ctx.first:
-            dw = conv_impl.first_wgrad(x, dy, m, out=g_w)      # x holds the saved patch matrix
-            dx = None
-        else:
-            dw = conv_impl.wgrad(x, dy, m, out=g_w)
-            dx = conv_impl.dgrad(dy, w_lp, m, x.shape) if ctx.needs_input_grad[0] else None
-        return (dx, _deliver(weight, g_w, dw),
-                _deliver(gamma, g_gamma, dgamma) if (gamma is not None and gamma.requires_grad) else None,
-                _deliver(beta, g_beta, dbeta) if beta is not None else None,
-                _deliver(bias, g_bias, dbias) if bias is not None else None,
-                dres, None, None)
+                _check(lib().b200_add_masked(_ptr(g), _ptr(dz), _ptr(mask3), _ptr(dx), g.numel(), _stream()), "add_masked")
+        elif proj:
+            svp = tuple(t[0:5]) + (False,)
+            _, _, gw, gg, gb, _ = _cb_backward(svp, dz, blk.shortcut, False, params[9], params[10], params[11], None,
+                                               False, False, gate=mask3)
+            grads[9:12] = [gw, gg, gb]
+        return (dx, None) + tuple(grads)
+
+
+def bottleneck_supported(blk) -> bool:
+    """The fused node covers the standard block: three conv+BN layers without bias, identity or conv+BN shortcut."""
+    convs = [blk.conv1, blk.conv2, blk.conv3]
+    sc = blk.shortcut
+    if sc is not None and not (hasattr(sc, "weight") and getattr(sc, "bn", None) is not None):
+        return False
+    if sc is not None:
+        convs.append(sc)
+    return all(m.bn is not None and m.bias is None and m.bn.gamma is not None and m.bn.beta is not None for m in convs)
+
+
+def bottleneck(x, blk):
+    params = []
+    for m in [blk.conv1, blk.conv2, blk.conv3] + ([blk.shortcut] if blk.shortcut is not None else []):
+        params += [m.weight, m.bn.gamma, m.bn.beta]
+    return _Bottleneck.apply(x, blk, *params)
 
 
 def conv_block(x, m, relu, residual=None):

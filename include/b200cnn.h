@@ -159,6 +159,11 @@ int b200_normalize_u8(const uint8_t* x, b200_bf16* y, int64_t pixels, int32_t c_
 
 /* out = a + b (bf16), n % 8 == 0. Used to sum the two gradient branches at a residual fork. */
 int b200_add(const b200_bf16* a, const b200_bf16* b, b200_bf16* out, int64_t n, void* stream);
+/* out = a + (mask bit ? b : 0), mask = one byte per 8 consecutive elements, bit k gates element k (the ReLU mask
+ * b200_bn_apply writes). Sums the two gradient branches at a residual fork when one of them still has to pass the
+ * block-output ReLU, without materialising the gated copy. n % 8 == 0. */
+int b200_add_masked(const b200_bf16* a, const b200_bf16* b, const uint8_t* mask, b200_bf16* out, int64_t n,
+                    void* stream);
 /* fp32 → bf16 cast of n elements. */
 int b200_cast_f32_bf16(const float* x, b200_bf16* y, int64_t n, void* stream);
 

@@ -234,3 +234,39 @@ def test_model_b200_path_matches_library_path(model, batch):
     # no single tensor is much worse than the stock bf16 path
     worst = min(m - l for m, l in zip(cm, c16))
     assert worst > -0.35, worst
+
+
+@pytest.mark.parametrize("in_c,depth,bott,stride", [(256, 256, 64, 1), (64, 256, 64, 1), (256, 512, 128, 2)])
+def test_fused_bottleneck_node_matches_chained_layers(in_c, depth, bott, stride, monkeypatch):
+    """The one-node bottleneck (ops/b200.py _Bottleneck: input-gradient sum fused with the output ReLU gate) against
+    the same block run as chained per-layer nodes. Both use the same kernels and round at the same points, so the
+    output, the input gradient and every parameter gradient must agree to bf16 rounding."""
+    from azure_hc_intel_tf_b200 import ops
+    from azure_hc_intel_tf_b200.models.builder import BuildConfig, ConvNetBuilder
+    from azure_hc_intel_tf_b200.models.resnet import Bottleneck
+    torch.manual_seed(3)
+    cfg = BuildConfig(kernels="b200")
+    cfg.use_batch_norm = True
+    cfg.bn_decay, cfg.bn_eps, cfg.bn_scale = 0.9, 1e-5, True
+    b = ConvNetBuilder(cfg, in_c, (28, 28))
+    blk = Bottleneck(b, depth, bott, stride, False).to(DEV)
+    blk.train()
+    x0 = nhwc_rand(4, in_c, 28, 28, 5)
+    dy = None
+    results = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("B200_FUSED_BLOCK", fused)
+        for p in blk.parameters():
+            p.grad = None
+        x = x0.clone().requires_grad_()
+        out = ops.bottleneck(x, blk)
+        if dy is None:
+            dy = nhwc_rand(*out.shape, 9)
+        out.backward(dy)
+        torch.cuda.synchronize()
+        results.append((out.detach().float(), x.grad.float(), [p.grad.float().clone() for p in blk.parameters()]))
+    (o1, g1, p1), (o0, g0, p0) = results
+    assert torch.equal(o1, o0)
+    assert torch.allclose(g1, g0, atol=1e-6, rtol=1e-6)
+    for a, c in zip(p1, p0):
+        assert torch.allclose(a, c, atol=1e-5, rtol=1e-5)
