@@ -277,10 +277,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else if (warp == 1 && cr == 0) {
     // ================================================================ MMA issuer (the pair's leader only)
     const uint32_t idesc = make_idesc_bf16(kBlockM * kCtas, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
-    auto mma = [](uint32_t d, uint64_t da, uint64_t db, uint32_t id, uint32_t accum) {
-      if constexpr (kCtas == 2) mma_bf16_pair(d, da, db, id, accum);
-      else mma_bf16(d, da, db, id, accum);
+    // descriptors: constant high word, low word stepped with adds (the issue rate of this one thread bounds tiles
+    // narrower than 256 columns)
+    const uint32_t d_hi = sdesc_hi_sw128(1024);
+    auto mma = [d_hi](uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t id, uint32_t accum) {
+      if constexpr (kCtas == 2) mma_bf16_pair_lohi(d, a_lo, d_hi, b_lo, d_hi, id, accum);
+      else mma_bf16_lohi(d, a_lo, d_hi, b_lo, d_hi, id, accum);
     };
+    const uint32_t b_lbo = p.b_mn_major ? (uint32_t)(kBlockK * 128) : 16u;   // MN-major: distance between 64-column chunks
+    const uint32_t b_kstep = p.b_mn_major ? (2048u >> 4) : (32u >> 4);        // descriptor step per 16 K elements
     auto commit = [](uint64_t* bar) {
       if constexpr (kCtas == 2) mma_commit_pair(bar);
       else mma_commit(bar);
@@ -303,17 +308,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           for (int tap = 0; tap < 9; ++tap) {
             const int r = tap / 3, s3 = tap - r * 3;
             // A rows of this tap: halo pixel (ty + r, tx + s): 8-pixel groups 16 halo pixels (2 KiB) apart
-            const uint32_t a0 = sh + (uint32_t)((r * kHaloCols + s3) * 128);
-            const uint32_t b0 = sbr + (uint32_t)(tap * b_bytes);
+            // the 128-byte swizzle is a function of the shared-memory address itself (measured: a window that starts
+            // s rows into a TMA-written tile reads correctly with base offset 0), so a shifted start needs no fix-up
+            const uint32_t a_lo = sdesc_lo(sh + (uint32_t)((r * kHaloCols + s3) * 128), 16);
+            const uint32_t b_lo = sdesc_lo(sbr + (uint32_t)(tap * b_bytes), b_lbo);
+            const uint32_t a_hi = sdesc_hi_sw128(kHaloCols * 128);
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k) {
-              // the 128-byte swizzle is a function of the shared-memory address itself (measured: a window that starts
-              // s rows into a TMA-written tile reads correctly with base offset 0), so a shifted start needs no fix-up
-              const uint64_t da = make_sdesc_sw128(a0 + k * 32, 16, kHaloCols * 128);
-              const uint64_t db = p.b_mn_major ? make_sdesc_sw128(b0 + k * 2048, kBlockK * 128, 1024)
-                                               : make_sdesc_sw128(b0 + k * 32, 16, 1024);
-              mma(d_tmem, da, db, idesc, (tap | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < kBlockK / 16; ++k)
+              mma_bf16_lohi(d_tmem, a_lo + k * 2, a_hi, b_lo + k * b_kstep, d_hi, idesc, (tap | k) != 0 ? 1u : 0u);
           }
           commit(&bars->empty[stage]);
           commit(&bars->tmem_full[acc]);
@@ -330,13 +332,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (lane == 0) {
           const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
           const uint32_t sb = p.b_resident ? smem_u32(bres) + (uint32_t)(kb * b_bytes) : sa + kABytes;
+          const uint32_t a_lo = sdesc_lo(sa, 16), b_lo = sdesc_lo(sb, b_lbo);
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            const uint64_t da = make_sdesc_sw128(sa + k * 32, 16, 1024);
-            const uint64_t db = p.b_mn_major ? make_sdesc_sw128(sb + k * 2048, kBlockK * 128, 1024)
-                                             : make_sdesc_sw128(sb + k * 32, 16, 1024);
-            mma(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 0; k < kBlockK / 16; ++k)
+            mma(d_tmem, a_lo + k * 2, b_lo + k * b_kstep, idesc, (kb | k) != 0 ? 1u : 0u);
           commit(&bars->empty[stage]);                           // frees the smem slot (in both CTAs of a pair)
           if (kb == p.num_k_blocks - 1) commit(&bars->tmem_full[acc]);
         }
