@@ -201,13 +201,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
           const uint32_t off0 = (uint32_t)((pl0 - plane_lo) * kHaloBytes + ((tap0 / 3) * kHaloCols + tap0 % 3) * 128);
           const uint32_t off1 = (uint32_t)((pl1 - plane_lo) * kHaloBytes + ((tap1 / 3) * kHaloCols + tap1 % 3) * 128);
           const uint32_t lbo = off1 > off0 ? off1 - off0 : 16;
+          // descriptor low words stepped with adds (the issue rate of this thread bounds the 64-wide tiles);
+          // shifted windows need no descriptor fix-up: the 128-byte swizzle follows the smem address (measured)
+          const uint32_t a_lo = sdesc_lo(sa + off0, lbo), a_hi = sdesc_hi_sw128(kHaloCols * 128);
+          const uint32_t b_lo = sdesc_lo(sb, kDyTileBytes), b_hi = sdesc_hi_sw128(1024);
+          const uint32_t d_t = tmem_base + (uint32_t)(t * p.block_n);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {                 // 16 pixels per step = output rows 2k, 2k+1 of the tile
-            // shifted windows need no descriptor fix-up: the 128-byte swizzle follows the smem address (measured)
-            const uint64_t da = make_sdesc_sw128(sa + off0 + (uint32_t)(2 * k * kHaloCols * 128), lbo, kHaloCols * 128);
-            const uint64_t db = make_sdesc_sw128(sb + k * 2048, kDyTileBytes, 1024);
-            mma_bf16(tmem_base + (uint32_t)(t * p.block_n), da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 0; k < 8; ++k)                   // 16 pixels per step = output rows 2k, 2k+1 of the tile
+            mma_bf16_lohi(d_t, a_lo + k * ((2 * kHaloCols * 128) >> 4), a_hi, b_lo + k * (2048 >> 4), b_hi, idesc,
+                          (kb | k) != 0 ? 1u : 0u);
         }
         mma_commit(&bars->empty[stage]);
         if (kb == nkb - 1) mma_commit(&bars->tmem_full);
@@ -228,13 +230,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
       if (lane == 0) {
         const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
         const uint32_t sb = sa + a_bytes;
+        const uint32_t a_lo = sdesc_lo(sa, kBox), b_lo = sdesc_lo(sb, kBox), d_hi = sdesc_hi_sw128(1024);
 #pragma unroll
         for (int k = 0; k < kBlockK / 16; ++k) {
-          const uint64_t db = make_sdesc_sw128(sb + k * 2048, kBox, 1024);
-          for (int t = 0; t < tiles_here; ++t) {
-            const uint64_t da = make_sdesc_sw128(sa + t * 2 * kBox + k * 2048, kBox, 1024);
-            mma_bf16(tmem_base + (uint32_t)(t * p.block_n), da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
+          for (int t = 0; t < tiles_here; ++t)
+            mma_bf16_lohi(tmem_base + (uint32_t)(t * p.block_n), a_lo + (uint32_t)((t * 2 * kBox + k * 2048) >> 4), d_hi,
+                          b_lo + k * (2048 >> 4), d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
         }
         mma_commit(&bars->empty[stage]);
         if (kb == nkb - 1) mma_commit(&bars->tmem_full);
