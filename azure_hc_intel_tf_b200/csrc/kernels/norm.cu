@@ -226,6 +226,15 @@ __global__ void __launch_bounds__(kThreads, 3) col_reduce_kernel(Policy pol, int
     const int nb = (int)gridDim.x;
     const int lo = (int)((int64_t)nb * sg / seg), hi = (int)((int64_t)nb * (sg + 1) / seg);
     int bk = lo;
+    // sixteen loads in flight per trip: this tail runs on one CTA while the rest of the GPU idles, so its length is
+    // the number of L2 round trips, not the bytes
+    for (; bk + 16 <= hi; bk += 16) {
+      float v[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + (size_t)(bk + u) * per_block + j);
+#pragma unroll
+      for (int u = 0; u < 16; ++u) acc += v[u];
+    }
     for (; bk + 4 <= hi; bk += 4) {
       const float v0 = __ldcg(base + (size_t)bk * per_block + j);
       const float v1 = __ldcg(base + (size_t)(bk + 1) * per_block + j);
