@@ -163,6 +163,39 @@ def w_nvl_allreduce(rank, world, sizes, iters):
     return out
 
 
+def w_nvl_flag_stress(rank, world, iters, seed):
+    """Flag-protocol stress: thousands of back-to-back collectives with no host synchronisation,
+    message sizes hopping across the one-shot / two-shot / NVLS switch points, and a random device-side delay in
+    front of every launch so the ranks arrive at the barriers in a different order each time. Every iteration each
+    rank overwrites its buffer with a fresh value, so a peer read that is one iteration stale (a barrier that let
+    someone through early) or a write that lands late shows up as a wrong sum. Mismatches are counted on the device."""
+    import random
+    import torch.distributed as dist
+    from .. import hvd
+    ctx = hvd.symmetric_context()
+    assert ctx is not None and hvd.fabric() == "nvl"
+    dev = hvd.device()
+    one_shot = ctx.one_shot_max_bytes // 4 if hasattr(ctx, "one_shot_max_bytes") else 32 * 1024
+    nvls = max(ctx.nvls_min_bytes // 4, 1 << 20) if hasattr(ctx, "nvls_min_bytes") else 2 << 20
+    sizes = [1024, one_shot, one_shot + 1024, 256 * 1024, nvls, nvls + 1024]
+    nmax = max(sizes)
+    buf = ctx.alloc_like_flat(nmax, torch.float32, multicast=True)
+    bad = torch.zeros((), dtype=torch.int64, device=dev)
+    rng = random.Random(seed * 131 + rank)          # per-rank delays
+    pick = random.Random(seed)                      # same size sequence on every rank
+    torch.cuda.synchronize()
+    dist.barrier()
+    for it in range(iters):
+        n = pick.choice(sizes)
+        torch.cuda._sleep(rng.randrange(0, 60_000))
+        buf.local[:n].fill_(float(rank + it % 97))
+        ctx.allreduce_range_(buf, 0, n, 1.0 / world)
+        expect = (it % 97) + (world - 1) / 2.0
+        bad += (buf.local[:n] != expect).sum()
+    torch.cuda.synchronize()
+    return int(bad.item())
+
+
 def w_nvl_fused_training(rank, world, steps, lars):
     """DistributedOptimizer on the nvl fabric (fused allreduce+SGD kernel) vs a single-process run on the
     concatenated batch; also returns whether ranks ended bit-identical."""

@@ -27,6 +27,15 @@ def test_p2p_allreduce_matches_nccl_and_is_rank_consistent():
 
 
 @needs2
+def test_flag_protocol_stress_with_random_delays():
+    """No host synchronisation, random per-rank delays, sizes hopping across the algorithm switch points."""
+    from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
+    world = min(_ngpu(), 8)
+    outs = testing.run_ranks(W.w_nvl_flag_stress, world, "nvl", args=(3000, 7), timeout=600)
+    assert outs == [0] * world, outs
+
+
+@needs2
 @pytest.mark.parametrize("lars", [False, True])
 def test_fused_allreduce_sgd_training_matches_single_process(lars):
     from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
