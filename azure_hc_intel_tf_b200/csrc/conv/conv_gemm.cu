@@ -115,7 +115,7 @@ __device__ long long g_trace[8];
 // kCtas == 2: the CTAs of a cluster pair share one 256-row tile (cta_group::2): CTA r stages rows [128 r, +128) of A
 // and rows/columns [r * block_n / 2, +block_n / 2) of the B tile; the leader (rank 0) owns the full / tmem_empty
 // barriers and issues the MMAs, both CTAs drain their own 128 TMEM lanes.
-template <int kCtas>
+template <int kCtas, bool kHalo>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_out, const GemmParams p) {
@@ -125,9 +125,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int bn_cta = p.block_n / kCtas;          // B rows (K-major) or columns (MN-major) staged by this CTA
   const int b_bytes = bn_cta * kBlockK * 2;
   // halo mode: [resident filter: 9 taps x b_bytes][stages x halo tile]; otherwise [stages x (A tile, B tile)]
-  const int stage_bytes = p.halo ? kHaloBytes : (p.b_resident ? kABytes : kABytes + b_bytes);
+  const int stage_bytes = kHalo ? kHaloBytes : (p.b_resident ? kABytes : kABytes + b_bytes);
   uint8_t* const bres = smem;
-  if (p.halo) smem += 9 * b_bytes;
+  if (kHalo) smem += 9 * b_bytes;
   if (p.b_resident) smem += p.num_k_blocks * b_bytes;
   uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;      // kOutBufs x 16 KiB when tma_store
   Barriers* bars = reinterpret_cast<Barriers*>(out_stage + (p.tma_store ? kOutBufs * kStageOutBytes : 0));
@@ -148,10 +148,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (p.tma_store) prefetch_tensormap(&map_out);
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&bars->full[i], 1);
-      mbar_init(&bars->empty[i], 1);
+      mbar_init(&bars->empty[i], kHalo ? 2 : 1);      // halo mode has two MMA-issuing warps (see halo_issue)
     }
     for (int i = 0; i < kAccStages; ++i) {
-      mbar_init(&bars->tmem_full[i], 1);
+      mbar_init(&bars->tmem_full[i], kHalo ? 2 : 1);
       // one arrive per epilogue warp that drains the stage: both groups of the pair when the tile has >= 2 boxes
       mbar_init(&bars->tmem_empty[i], ((p.tma_store && p.block_n >= 128) ? 8 : 4) * kCtas);
     }
@@ -174,9 +174,57 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     else tma_load_2d(dst, map, bar, c0, c1);
   };
 
+  // Halo mode, MMA issue: the 36 MMAs of a tile are 64 columns wide (32 cycles of math each) and one thread cannot
+  // issue them faster than ~78 cycles apiece, so TWO warps issue: warp 1 takes taps [0, 5) into accumulator columns
+  // [0, 64) of the stage, warp 6 (an epilogue warp that has no box to drain in this mode) takes taps [5, 9) into
+  // columns [64, 128); the epilogue adds the two partial accumulators. Both wait on the same full / tmem_empty
+  // barriers and both commit to empty / tmem_full (count 2).
+  auto halo_issue = [&](int tap_lo, int tap_hi, uint32_t col_off) {
+    const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
+    const uint32_t d_hi = sdesc_hi_sw128(1024), a_hi = sdesc_hi_sw128(kHaloCols * 128);
+    const uint32_t b_lbo = p.b_mn_major ? (uint32_t)(kBlockK * 128) : 16u;
+    const uint32_t b_kstep = p.b_mn_major ? (2048u >> 4) : (32u >> 4);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    mbar_wait(&bars->bres, 0);
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+      mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN) + col_off;
+      mbar_wait(&bars->full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sh = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t sbr = smem_u32(bres);
+        for (int tap = tap_lo; tap < tap_hi; ++tap) {
+          const int r = tap / 3, s3 = tap - r * 3;
+          // A rows of this tap: halo pixel (ty + r, tx + s): 8-pixel groups 16 halo pixels (2 KiB) apart. The
+          // 128-byte swizzle is a function of the shared-memory address itself (measured: a window that starts s rows
+          // into a TMA-written tile reads correctly with base offset 0), so a shifted start needs no fix-up
+          const uint32_t a_lo = sdesc_lo(sh + (uint32_t)((r * kHaloCols + s3) * 128), 16);
+          const uint32_t b_lo = sdesc_lo(sbr + (uint32_t)(tap * b_bytes), b_lbo);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k)
+            mma_bf16_lohi(d_tmem, a_lo + k * 2, a_hi, b_lo + k * b_kstep, d_hi, idesc, (tap != tap_lo || k != 0) ? 1u : 0u);
+        }
+        mma_commit(&bars->empty[stage]);
+        mma_commit(&bars->tmem_full[acc]);
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+      if (++acc == kAccStages) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  };
+
   if (warp == 0) {
     // ================================================================ TMA producer
-    if (lane == 0 && p.halo) {
+    if (lane == 0 && kHalo) {
       // filter of this CTA's N tile (gridDim.x is a multiple of num_n_tiles, so the N tile never changes): resident
       const int nt0 = blockIdx.x % p.num_n_tiles, n00 = nt0 * p.block_n;
       mbar_expect_tx(&bars->bres, (uint32_t)(9 * b_bytes));
@@ -276,6 +324,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   } else if (warp == 1 && cr == 0) {
     // ================================================================ MMA issuer (the pair's leader only)
+    if (kHalo) halo_issue(0, 5, 0);
     const uint32_t idesc = make_idesc_bf16(kBlockM * kCtas, (uint32_t)p.block_n, 0, (uint32_t)p.b_mn_major);
     // descriptors: constant high word, low word stepped with adds (the issue rate of this one thread bounds tiles
     // narrower than 256 columns)
@@ -294,39 +343,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    if (p.halo || p.b_resident) mbar_wait(&bars->bres, 0);
-    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+    if (p.b_resident) mbar_wait(&bars->bres, 0);
+    for (int tile = tile_first; tile < (kHalo ? 0 : num_tiles); tile += tile_step) {
       TRACED_WAIT(1, mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1));
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kMaxBlockN);
-      if (p.halo) {
-        mbar_wait(&bars->full[stage], phase);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sh = smem_u32(smem + (size_t)stage * stage_bytes);
-          const uint32_t sbr = smem_u32(bres);
-          for (int tap = 0; tap < 9; ++tap) {
-            const int r = tap / 3, s3 = tap - r * 3;
-            // A rows of this tap: halo pixel (ty + r, tx + s): 8-pixel groups 16 halo pixels (2 KiB) apart
-            // the 128-byte swizzle is a function of the shared-memory address itself (measured: a window that starts
-            // s rows into a TMA-written tile reads correctly with base offset 0), so a shifted start needs no fix-up
-            const uint32_t a_lo = sdesc_lo(sh + (uint32_t)((r * kHaloCols + s3) * 128), 16);
-            const uint32_t b_lo = sdesc_lo(sbr + (uint32_t)(tap * b_bytes), b_lbo);
-            const uint32_t a_hi = sdesc_hi_sw128(kHaloCols * 128);
-#pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              mma_bf16_lohi(d_tmem, a_lo + k * 2, a_hi, b_lo + k * b_kstep, d_hi, idesc, (tap | k) != 0 ? 1u : 0u);
-          }
-          commit(&bars->empty[stage]);
-          commit(&bars->tmem_full[acc]);
-        }
-        __syncwarp();
-        if (++stage == p.stages) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      for (int kb = 0; kb < (p.halo ? 0 : p.num_k_blocks); ++kb) {
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         TRACED_WAIT(2, mbar_wait(&bars->full[stage], phase));
         tc_fence_after();
         if (lane == 0) {
@@ -371,6 +393,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       __threadfence_block();
       asm volatile("bar.sync %0, 256;" ::"r"(6 + acc) : "memory");
     }
+    if (kHalo && warp == 6) halo_issue(5, 9, 64);      // second MMA-issuing warp of halo mode (its group has no box)
     if (p.tma_store) {
       // ---- staged path: TMEM -> registers -> bf16 -> swizzled shared memory -> TMA bulk store (or cooperative
       //      scatter); BatchNorm statistics are taken from the staged (stored) values with conflict-free reads.
@@ -400,7 +423,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           continue;
         }
         int h_img = 0, h_y0 = 0, h_x0 = 0;           // halo mode: image and top-left output pixel of this tile
-        if (p.halo) {
+        if (kHalo) {
           const int per_img = p.tiles_x * p.tiles_y;
           h_img = mt / per_img;
           const int rem = mt - h_img * per_img;
@@ -427,8 +450,21 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t r[32];
-            tmem_ld_x32(t_row + (uint32_t)(bx * 64 + half * 32), r);
-            tmem_ld_wait();
+            if (kHalo) {
+              // two partial accumulators (one per issuing warp): columns [0, 64) and [64, 128) of the stage
+#pragma unroll
+              for (int q = 0; q < 2; ++q) {
+                uint32_t ra[16], rb[16];
+                tmem_ld_x16(t_row + (uint32_t)(half * 32 + q * 16), ra);
+                tmem_ld_x16(t_row + (uint32_t)(64 + half * 32 + q * 16), rb);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) r[q * 16 + j] = __float_as_uint(__uint_as_float(ra[j]) + __uint_as_float(rb[j]));
+              }
+            } else {
+              tmem_ld_x32(t_row + (uint32_t)(bx * 64 + half * 32), r);
+              tmem_ld_wait();
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {       // four 16-byte chunks of 8 bf16
               __nv_bfloat162 t;
@@ -456,7 +492,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           if (!p.scatter) {
             if (et == 0) {
-              if (p.halo)
+              if (kHalo)
                 tma_store_4d(&map_out, buf, n0 + bx * 64, h_x0, h_y0, h_img);   // 16 x 8 pixels; clipped at the edges
               else
                 tma_store_2d(&map_out, buf, n0 + bx * 64, mt * kBlockM);
@@ -494,7 +530,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             for (int i = 0; i < 32; ++i) {
               const int row = qtr * 32 + i;
               // halo tiles may hang over the image edge: those rows hold values that are never stored
-              if (p.halo && (h_y0 + (row >> 3) >= p.Himg || h_x0 + (row & 7) >= p.Wimg)) continue;
+              if (kHalo && (h_y0 + (row >> 3) >= p.Himg || h_x0 + (row & 7) >= p.Wimg)) continue;
               const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4) + word * 4);
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
               s1a += f.x;
@@ -678,12 +714,12 @@ int plan_grid(int num_m_tiles, int num_n_tiles, int ctas) {
   return (groups < max_groups ? groups : max_groups) * ctas;
 }
 
-template <int kCtas>
+template <int kCtas, bool kHalo>
 cudaError_t launch_kernel(int grid, size_t smem, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb,
                           const CUtensorMap& mo, const GemmParams& p) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<kCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<kCtas, kHalo>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
@@ -699,7 +735,7 @@ cudaError_t launch_kernel(int grid, size_t smem, cudaStream_t st, const CUtensor
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = kCtas > 1 ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, conv_gemm_kernel<kCtas>, ma, mb, mo, p);
+  return cudaLaunchKernelEx(&cfg, conv_gemm_kernel<kCtas, kHalo>, ma, mb, mo, p);
 }
 
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStream_t st) {
@@ -755,8 +791,9 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
     B200_CUDA(cudaMemsetAsync(trace_buf, 0, 8 * sizeof(long long), st));
     p.trace = trace_buf;
   }
-  if (p.ctas == 2) B200_CUDA(launch_kernel<2>(grid, smem, st, ma, mb, mo, p));
-  else B200_CUDA(launch_kernel<1>(grid, smem, st, ma, mb, mo, p));
+  if (p.halo) B200_CUDA((launch_kernel<1, true>(grid, smem, st, ma, mb, mo, p)));
+  else if (p.ctas == 2) B200_CUDA((launch_kernel<2, false>(grid, smem, st, ma, mb, mo, p)));
+  else B200_CUDA((launch_kernel<1, false>(grid, smem, st, ma, mb, mo, p)));
   B200_LAUNCH_CHECK();
   if (trace_on) {
     long long h[8];
