@@ -1,5 +1,9 @@
 // mma_rate.cu - cycles per tcgen05.mma (bf16, M=128, K=16, SS operands, 128B swizzle) as a function of N and operand
-// majorness, with nothing else touching shared memory. Build: nvcc -gencode arch=compute_100a,code=sm_100a -I../../azure_hc_intel_tf_b200/csrc -I../../include
+// majorness, with nothing else touching shared memory. Measured on B200 (148 CTAs, one per SM):
+//   N=256: 128.0 cycles = the tensor-pipe floor, in every mode.
+//   N<=128: 96 cycles with descriptors rebuilt per MMA, 78 with stepped descriptor words, 99.5 when a tcgen05.commit
+//   follows every fourth MMA - i.e. each tcgen05 instruction costs the one issuing thread ~80 cycles, more than the
+//   32 / 64 cycles of math of a 64 / 128-column MMA. Hence the second issuing warp of the halo mode in conv_gemm.cu. Build: nvcc -gencode arch=compute_100a,code=sm_100a -I../../azure_hc_intel_tf_b200/csrc -I../../include
 #include <cstdio>
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -11,11 +15,13 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int n, int a_mn, int b_mn,
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
+  __shared__ uint64_t bar2;
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < 200 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
   if (threadIdx.x == 0) {
     mbar_init(&bar, 1);
+    mbar_init(&bar2, 1);
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc<512>(&tmem_slot);
@@ -37,6 +43,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int n, int a_mn, int b_mn,
         const uint32_t a_step = a_mn ? 128u : 2u, b_step = b_mn ? 128u : 2u, hi = sdesc_hi_sw128(1024);
 #pragma unroll
         for (int k = 0; k < 4; ++k) mma_bf16_lohi(tmem, a_lo + k * a_step, hi, b_lo + k * b_step, hi, idesc, (it | k) ? 1u : 0u);
+        if (fast == 2) mma_commit(&bar2);      // a tcgen05.commit per k-block, as the pipelined kernels do
         continue;
       }
 #pragma unroll
@@ -63,7 +70,7 @@ int main() {
   cudaMalloc(&d, 8);
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
   const int iters = 4000;
-  for (int fast : {0, 1})
+  for (int fast : {0, 1, 2})
     for (int n : {64, 128, 256})
       for (int mode = 0; mode < 4; mode += 3) {
         const int grid = 148;
@@ -72,7 +79,7 @@ int main() {
         rate_kernel<<<grid, 128, 210 * 1024>>>(n, a_mn, b_mn, iters, kblocks, fast, d);
         long long h = 0;
         cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
-        printf("%s grid %3d N=%3d A %s B %s: %.1f cycles per MMA (nominal %d)%s\n", fast ? "stepped-desc" : "rebuilt-desc", grid, n, a_mn ? "MN" : "K ", b_mn ? "MN" : "K ",
+        printf("%s grid %3d N=%3d A %s B %s: %.1f cycles per MMA (nominal %d)%s\n", fast == 2 ? "stepped+commit" : (fast ? "stepped-desc  " : "rebuilt-desc  "), grid, n, a_mn ? "MN" : "K ", b_mn ? "MN" : "K ",
                (double)h / (iters * 4.0), n / 2, e == cudaSuccess ? "" : cudaGetErrorString(e));
       }
   return 0;
