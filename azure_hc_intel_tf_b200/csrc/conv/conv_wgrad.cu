@@ -93,15 +93,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   int kb1 = kb0 + p.kblocks_per_slice;
   if (kb1 > p.kblocks_total) kb1 = p.kblocks_total;
   const int nkb = kb1 - kb0;        // >= 1 by construction
+  const bool dual = p.block_n <= 128;                        // two issuing warps (see issue_halo / issue_generic)
+  const int t_split = dual ? (tiles_here + 1) / 2 : tiles_here;
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&map_x);
     prefetch_tensormap(&map_dy);
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&bars->full[i], 1);
-      mbar_init(&bars->empty[i], 1);
+      mbar_init(&bars->empty[i], dual ? 2 : 1);
     }
-    mbar_init(&bars->tmem_full, 1);
+    mbar_init(&bars->tmem_full, dual ? 2 : 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<kTmemCols>(&bars->tmem_base);
@@ -116,6 +118,77 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
   if (pos_hi > 9 * p.cchunks - 1) pos_hi = 9 * p.cchunks - 1;
   const int plane_lo = p.halo ? pos_lo / 9 : 0;
   const int nplanes = p.halo ? pos_hi / 9 - plane_lo + 1 : 0;
+
+  // MMA issue. Tiles of at most 128 columns are bound by the issue rate of one thread (~80 cycles per tcgen05
+  // instruction against 32-64 cycles of math, scripts/micro/mma_rate.cu), so for those a second warp issues too: the
+  // M tiles of this CTA (each with its own accumulator columns) are split between warp 1 and warp 2; both wait on the
+  // same full barriers and both commit to empty / tmem_full (count 2). Warp 2 joins the epilogue afterwards.
+  auto issue_halo = [&](int t_lo, int t_hi) {
+    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(&bars->full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t sb = sa + a_bytes;
+        for (int t = t_lo; t < t_hi; ++t) {
+          // the two 64-row halves of M tile t: positions 2t and 2t+1 of the (plane, tap) space
+          const int p0 = 2 * (tile0 + t);
+          int p1 = p0 + 1;
+          if (p1 > 9 * p.cchunks - 1) p1 = p0;          // odd tail: second half is masked in the epilogue
+          const int pl0 = p0 / 9, tap0 = p0 - pl0 * 9, pl1 = p1 / 9, tap1 = p1 - pl1 * 9;
+          const uint32_t off0 = (uint32_t)((pl0 - plane_lo) * kHaloBytes + ((tap0 / 3) * kHaloCols + tap0 % 3) * 128);
+          const uint32_t off1 = (uint32_t)((pl1 - plane_lo) * kHaloBytes + ((tap1 / 3) * kHaloCols + tap1 % 3) * 128);
+          const uint32_t lbo = off1 > off0 ? off1 - off0 : 16;
+          // descriptor low words stepped with adds (the issue rate of this thread bounds the 64-wide tiles);
+          // shifted windows need no descriptor fix-up: the 128-byte swizzle follows the smem address (measured)
+          const uint32_t a_lo = sdesc_lo(sa + off0, lbo), a_hi = sdesc_hi_sw128(kHaloCols * 128);
+          const uint32_t b_lo = sdesc_lo(sb, kDyTileBytes), b_hi = sdesc_hi_sw128(1024);
+          const uint32_t d_t = tmem_base + (uint32_t)(t * p.block_n);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)                   // 16 pixels per step = output rows 2k, 2k+1 of the tile
+            mma_bf16_lohi(d_t, a_lo + k * ((2 * kHaloCols * 128) >> 4), a_hi, b_lo + k * (2048 >> 4), b_hi, idesc,
+                          (kb | k) != 0 ? 1u : 0u);
+        }
+        mma_commit(&bars->empty[stage]);
+        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  };
+  auto issue_generic = [&](int t_lo, int t_hi) {
+    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(&bars->full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t sb = sa + a_bytes;
+        const uint32_t a_lo = sdesc_lo(sa, kBox), b_lo = sdesc_lo(sb, kBox), d_hi = sdesc_hi_sw128(1024);
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          for (int t = t_lo; t < t_hi; ++t)
+            mma_bf16_lohi(tmem_base + (uint32_t)(t * p.block_n), a_lo + (uint32_t)((t * 2 * kBox + k * 2048) >> 4), d_hi,
+                          b_lo + k * (2048 >> 4), d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        mma_commit(&bars->empty[stage]);
+        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  };
 
   if (warp == 0 && p.halo) {
     if (lane == 0) {
@@ -182,71 +255,14 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         }
       }
     }
-  } else if (warp == 1 && p.halo) {
-    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = 0; kb < nkb; ++kb) {
-      mbar_wait(&bars->full[stage], phase);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
-        const uint32_t sb = sa + a_bytes;
-        for (int t = 0; t < tiles_here; ++t) {
-          // the two 64-row halves of M tile t: positions 2t and 2t+1 of the (plane, tap) space
-          const int p0 = 2 * (tile0 + t);
-          int p1 = p0 + 1;
-          if (p1 > 9 * p.cchunks - 1) p1 = p0;          // odd tail: second half is masked in the epilogue
-          const int pl0 = p0 / 9, tap0 = p0 - pl0 * 9, pl1 = p1 / 9, tap1 = p1 - pl1 * 9;
-          const uint32_t off0 = (uint32_t)((pl0 - plane_lo) * kHaloBytes + ((tap0 / 3) * kHaloCols + tap0 % 3) * 128);
-          const uint32_t off1 = (uint32_t)((pl1 - plane_lo) * kHaloBytes + ((tap1 / 3) * kHaloCols + tap1 % 3) * 128);
-          const uint32_t lbo = off1 > off0 ? off1 - off0 : 16;
-          // descriptor low words stepped with adds (the issue rate of this thread bounds the 64-wide tiles);
-          // shifted windows need no descriptor fix-up: the 128-byte swizzle follows the smem address (measured)
-          const uint32_t a_lo = sdesc_lo(sa + off0, lbo), a_hi = sdesc_hi_sw128(kHaloCols * 128);
-          const uint32_t b_lo = sdesc_lo(sb, kDyTileBytes), b_hi = sdesc_hi_sw128(1024);
-          const uint32_t d_t = tmem_base + (uint32_t)(t * p.block_n);
-#pragma unroll
-          for (int k = 0; k < 8; ++k)                   // 16 pixels per step = output rows 2k, 2k+1 of the tile
-            mma_bf16_lohi(d_t, a_lo + k * ((2 * kHaloCols * 128) >> 4), a_hi, b_lo + k * (2048 >> 4), b_hi, idesc,
-                          (kb | k) != 0 ? 1u : 0u);
-        }
-        mma_commit(&bars->empty[stage]);
-        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
-      }
-      __syncwarp();
-      if (++stage == p.stages) {
-        stage = 0;
-        phase ^= 1;
-      }
-    }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.block_n, 1, 1);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = 0; kb < nkb; ++kb) {
-      mbar_wait(&bars->full[stage], phase);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
-        const uint32_t sb = sa + a_bytes;
-        const uint32_t a_lo = sdesc_lo(sa, kBox), b_lo = sdesc_lo(sb, kBox), d_hi = sdesc_hi_sw128(1024);
-#pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k) {
-          for (int t = 0; t < tiles_here; ++t)
-            mma_bf16_lohi(tmem_base + (uint32_t)(t * p.block_n), a_lo + (uint32_t)((t * 2 * kBox + k * 2048) >> 4), d_hi,
-                          b_lo + k * (2048 >> 4), d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
-        }
-        mma_commit(&bars->empty[stage]);
-        if (kb == nkb - 1) mma_commit(&bars->tmem_full);
-      }
-      __syncwarp();
-      if (++stage == p.stages) {
-        stage = 0;
-        phase ^= 1;
-      }
-    }
+    if (p.halo) issue_halo(0, t_split);
+    else issue_generic(0, t_split);
   } else {
+    if (dual && warp == 2) {
+      if (p.halo) issue_halo(t_split, tiles_here);
+      else issue_generic(t_split, tiles_here);
+    }
     const int lane_group = warp & 3;            // TMEM lanes [32*lane_group, +32) are visible to this warp
     const int col_half = (warp - 2) >> 2;       // eight epilogue warps: two per lane group
     mbar_wait_backoff(&bars->tmem_full, 0);
