@@ -44,6 +44,7 @@ SIGS = {
     "b200_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
 }
 
+# conv / GEMM era entry points (kept in a second table only for readability)
 OPTIONAL = {
     "b200_bn_stats_noalloc": (i32, [vp, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
     "b200_bn_stats_noalloc_max_bytes": (i64, []),
@@ -71,9 +72,10 @@ def declare(lib):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    # every entry point is required: a library that lacks one is stale or mis-built, and silently routing its callers
+    # to a fallback would hide that (tests/test_abi.py checks headers, signatures and exports against each other)
     for name, (res, args) in OPTIONAL.items():
-        fn = getattr(lib, name, None)
-        if fn is not None:
-            fn.restype = res
-            fn.argtypes = args
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
     return lib

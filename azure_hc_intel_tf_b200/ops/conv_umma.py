@@ -42,11 +42,11 @@ def supports_dgrad(dy, w_lp, m, x_shape) -> bool:
 
 
 def supports_wgrad(x, dy, m) -> bool:
-    return hasattr(lib(), "b200_conv_wgrad") and _ok(geom(x.shape, m), WGRAD, "wgrad")
+    return _ok(geom(x.shape, m), WGRAD, "wgrad")
 
 
 def supports_gemm(m_, n_, k_) -> bool:
-    return "gemm" not in _disabled and k_ % 64 == 0 and hasattr(lib(), "b200_gemm_nt")
+    return "gemm" not in _disabled and k_ % 64 == 0
 
 
 def fprop(x, w_lp, m, want_stats: bool = False):
@@ -134,7 +134,7 @@ def dense_wgrad(x, dy, out_features, out=None):
 # ------------------------------------------------------------------------------------ first layer (Cin = 3)
 
 def supports_first_layer(x, m) -> bool:
-    return "first" not in _disabled and m.cin < 8 and m.cout % 8 == 0 and hasattr(lib(), "b200_im2col_small_c")
+    return "first" not in _disabled and m.cin < 8 and m.cout % 8 == 0
 
 
 def first_layer_kpad(m) -> int:
