@@ -49,6 +49,7 @@ OPTIONAL = {
     "b200_bn_stats_noalloc": (i32, [vp, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
     "b200_bn_stats_noalloc_max_bytes": (i64, []),
     "b200_conv_supported": (i32, [C.POINTER(ConvGeom), i32]),
+    "b200_conv_min_channels": (i32, []),
     "b200_conv_fprop": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
     "b200_conv_stats_rows": (i64, [C.POINTER(ConvGeom)]),
     "b200_conv_stats_first_result_row": (i64, [C.POINTER(ConvGeom)]),

@@ -30,6 +30,10 @@ enum { B200_CONV_FPROP = 0, B200_CONV_DGRAD = 1, B200_CONV_WGRAD = 2 };
 /* 1 if the tensor-core kernel covers this geometry for `op`, else 0 (callers fall back to a library). */
 int b200_conv_supported(const b200_conv_geom* g, int op);
 
+/* Smallest input-channel count b200_conv_supported accepts (default 64: thinner layers compute correctly through TMA
+ * zero-fill but measured slower than the library; environment B200_CONV_MIN_C overrides, read once). */
+int b200_conv_min_channels(void);
+
 /* y[n,p,q,k] = sum_{r,s,c} x[n, p*sh - pad_t + r, q*sw - pad_l + s, c] * w[k,r,s,c].
  * col_stats (optional): [b200_conv_stats_rows(g)][2][k] fp32 buffer for the batch-norm statistics of the stored
  * (bf16-rounded) outputs, produced by the epilogue so that y is not read again. The first

@@ -68,3 +68,17 @@ def test_dry_run_prints_command():
 def test_shell_wrapper_exists_and_is_executable():
     p = os.path.join(os.path.dirname(os.path.dirname(__file__)), "launch", "run-tf-b200.sh")
     assert os.access(p, os.X_OK)
+
+
+def test_environment_report_runs_without_a_gpu():
+    """utils/doctor.py = the reference images' %runscript sanity print (tf-hvd-gcc-ompi-ucx-mlnx.def:45-55) plus the
+    update_config.sh limits, checked instead of set. On a CPU-only box it must come out 'ready' for the plumbing path."""
+    from azure_hc_intel_tf_b200.utils import doctor
+    lines, fail = doctor.collect()
+    text = "\n".join(lines)
+    for key in ("OS", "python", "g++", "torch", "libhvd_core.so", "libb200cnn.so", "ulimit nofile"):
+        assert key in text, key
+    import torch
+    if not torch.cuda.is_available():
+        assert fail == [], fail
+        assert "CPU plumbing" in text
