@@ -175,14 +175,14 @@ class BenchmarkCNN:
         p = self.p
         dev = "gpu" if self.device.type == "cuda" else "cpu"
         devices = [f"horovod/{dev}:{i}" for i in range(self.world)] if self.use_hvd else [f"/{dev}:0"]
-        n_img = 1281167
+        n_img = 50000 if p.data_name == "cifar10" else 1281167       # training-set sizes tf_cnn_benchmarks reports epochs against
         extra = []
         if self.use_hvd:
             extra.append(f"Horovod on:  {dev}")
             extra.append(f"Fabric:      {self.fabric}")
         extra.append(f"Kernels:     {self.kernels}")
         extra.append(f"Precision:   {'bf16' if self.dtype == torch.bfloat16 else 'fp32'}")
-        lines = log.header_lines(self.model.name, "imagenet (synthetic)",
+        lines = log.header_lines(self.model.name, f"{p.data_name} (synthetic)",
                                  "forward-only" if p.forward_only else "training", self.global_batch, self.batch,
                                  p.num_batches, p.num_batches * self.global_batch / n_img, devices,
                                  "NHWC" if self.device.type == "cuda" else p.data_format, p.optimizer,

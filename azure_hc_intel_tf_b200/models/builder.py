@@ -129,6 +129,19 @@ class BatchNorm(nn.Module):
         self.tf_buffers = {"moving_mean": f"{scope}/moving_mean", "moving_variance": f"{scope}/moving_variance"}
 
 
+class BNAct(nn.Module):
+    """Standalone batch-norm (+ReLU): ``ConvNetBuilder.batch_norm`` — the pre-activation of ResNet v2 / DenseNet."""
+
+    def __init__(self, cfg: BuildConfig, c: int, scope: str, activation: Optional[str]):
+        super().__init__()
+        self.cfg = cfg
+        self.bn = BatchNorm(cfg, c, scope)
+        self.activation = activation
+
+    def forward(self, x):
+        return ops.batch_norm(x, self.bn, relu=self.activation == "relu")
+
+
 class Affine(nn.Module):
     """Fully connected layer (``ConvNetBuilder.affine``). Weights are stored (out, in); TF layout is (in, out)."""
 
@@ -250,6 +263,11 @@ class ConvNetBuilder:
         if advance:
             self.c, self.hw = cout, m.out_hw
         return m
+
+    def batch_norm(self, activation: Optional[str] = "relu", c: Optional[int] = None) -> BNAct:
+        scope = "/".join([self.prefix] + self.scope_stack + [f"batchnorm{self.counts['batchnorm']}"])
+        self.counts["batchnorm"] += 1
+        return BNAct(self.cfg, self.c if c is None else c, scope, activation)
 
     def mpool(self, k: IntPair, stride: IntPair = 2, mode: str = "VALID", in_hw=None, advance=True) -> Pool:
         self.counts["mpool"] += 1

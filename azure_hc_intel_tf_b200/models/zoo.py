@@ -1,4 +1,5 @@
-"""VGG, Inception-v3, GoogLeNet, AlexNet, trivial — the rest of the tf_cnn_benchmarks zoo the harness can
+"""VGG, Inception-v3, GoogLeNet, AlexNet, trivial (and, in zoo2.py, ResNet v2, the CIFAR-10 ResNets / DenseNets and
+Inception-v4) — the rest of the tf_cnn_benchmarks zoo the harness can
 name with ``--model`` (the reference hard-codes resnet50 at run-tf-sing-ucx-openmpi.sh:34 and tells the
 user to edit the script for others; BASELINE.json configs add VGG-16 and Inception-v3).
 """

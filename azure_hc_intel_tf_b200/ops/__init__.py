@@ -21,6 +21,12 @@ def _b200():
     return b200
 
 
+def _vec8(c: int) -> bool:
+    """The sm_100a kernels move 8-channel (16-byte) vectors; layers whose channel count is not a multiple of 8
+    (DenseNet growth 12, CIFAR stems) take the stock ops instead."""
+    return c % 8 == 0
+
+
 def _sym(pad):
     (pt, pb), (pl, pr) = pad
     return pt == pb and pl == pr
@@ -30,13 +36,15 @@ def _sym(pad):
 
 def conv_block(x, m, relu: bool):
     """conv (+bias) (+training-mode batch-norm) (+ReLU)."""
-    if m.cfg.kernels == "b200":
+    if m.cfg.kernels == "b200" and _vec8(m.cout) and (_vec8(m.cin) or m.cin < 8):
         return _b200().conv_block(x, m, relu)
     (pt, pb), (pl, pr) = m.pad
+    w = m.weight if m.weight.dtype == x.dtype else m.weight.to(x.dtype)
+    bias = None if (m.bn is not None or m.bias is None) else m.bias.to(x.dtype)
     if _sym(m.pad):
-        y = F.conv2d(x, m.weight, None if m.bn is not None else m.bias, m.stride, (pt, pl))
+        y = F.conv2d(x, w, bias, m.stride, (pt, pl))
     else:
-        y = F.conv2d(F.pad(x, (pl, pr, pt, pb)), m.weight, None if m.bn is not None else m.bias, m.stride)
+        y = F.conv2d(F.pad(x, (pl, pr, pt, pb)), w, bias, m.stride)
     if m.bn is not None:
         y = batch_norm(y, m.bn, relu=relu)
     elif relu:
@@ -46,7 +54,7 @@ def conv_block(x, m, relu: bool):
 
 def batch_norm(y, bn, relu: bool = False, residual=None):
     """Training-mode BN; optional fused residual add and ReLU (y = relu(bn(y) + residual))."""
-    if bn.cfg.kernels == "b200":
+    if bn.cfg.kernels == "b200" and _vec8(y.shape[1]) and y.dim() == 4:
         return _b200().batch_norm(y, bn, relu, residual)
     out = F.batch_norm(y, bn.moving_mean, bn.moving_variance, bn.gamma, bn.beta, bn.training,
                        1.0 - bn.decay, bn.eps)
@@ -93,7 +101,7 @@ def affine(x, m, relu: bool):
 
 
 def pool(x, m):
-    if m.cfg.kernels == "b200":
+    if m.cfg.kernels == "b200" and _vec8(x.shape[1]):
         return _b200().pool(x, m)
     (pt, pb), (pl, pr) = m.pad
     if m.kind == "max":
@@ -110,7 +118,7 @@ def pool(x, m):
 
 
 def spatial_mean(x, cfg):
-    if cfg.kernels == "b200":
+    if cfg.kernels == "b200" and _vec8(x.shape[1]):
         return _b200().spatial_mean(x)
     return x.mean(dim=(2, 3))
 

@@ -158,8 +158,13 @@ def validate(p: Params) -> None:
             f"--variable_update={p.variable_update} is a parameter-server / in-graph replication mode of "
             f"tf_cnn_benchmarks that the reference never uses (it passes horovod); supported: "
             f"{SUPPORTED_VARIABLE_UPDATES}")
-    if p.data_name != "imagenet":
-        raise SystemExit("only --data_name=imagenet is supported")
+    if p.data_name not in ("imagenet", "cifar10"):
+        raise SystemExit("--data_name must be imagenet or cifar10 (synthetic data of that shape)")
+    from ..models import dataset_of, available_models
+    if p.model in available_models() and dataset_of(p.model) != p.data_name:
+        want = dataset_of(p.model)
+        p.notes.append(f"--model={p.model} is a {want} model: --data_name={p.data_name} replaced by {want}")
+        p.data_name = want
     if p.data_dir:
         p.notes.append(f"--data_dir={p.data_dir} ignored: no dataset on this box, synthetic ImageNet is used")
         p.data_dir = None

@@ -12,6 +12,11 @@ from azure_hc_intel_tf_b200.models import available_models, create_model
 EXPECTED_PARAMS = {          # trainable parameters with 1001 classes
     "resnet50": 25559081, "resnet101": 44551209, "resnet152": 60194857, "vgg16": 138361641, "vgg19": 143671337,
     "inception3": 23819401, "googlenet": 6999577, "alexnet": 61842345,
+    "resnet50_v2": 25551529, "inception4": 42649769,
+    # CIFAR-10 models (11 classes): the published sizes are 0.27 M / 0.85 M / 1.7 M (ResNet-20/56/110) and
+    # 1.0 M / 7.0 M / 27.2 M (DenseNet 40-k12 / 100-k12 / 100-k24)
+    "resnet20": 269787, "resnet56": 853083, "resnet110": 1728027, "resnet20_v2": 269787,
+    "densenet40_k12": 1020171, "densenet100_k12": 6980811, "densenet100_k24": 27251403,
 }
 
 
@@ -28,14 +33,34 @@ def test_resnet50_has_161_trainable_tensors_and_53_convs():
     assert sum(1 for x in m.modules() if isinstance(x, Conv)) == 53
 
 
-@pytest.mark.parametrize("name", ["resnet50", "googlenet", "lenet", "trivial"])
+@pytest.mark.parametrize("name", ["resnet50", "googlenet", "lenet", "trivial", "resnet50_v2", "resnet20", "resnet32_v2",
+                                  "densenet40_k12", "inception4"])
 def test_forward_backward_shapes(name):
     m = create_model(name)
     x = torch.randn(2, 3, m.image_size, m.image_size).contiguous(memory_format=torch.channels_last)
     y = m(x)
-    assert y.shape == (2, 1001)
+    assert y.shape == (2, m.cfg.num_classes)
+    assert m.cfg.num_classes == (11 if m.image_size == 32 else 1001)
     y.sum().backward()
     assert all(p.grad is not None for p in m.parameters() if p.requires_grad)
+
+
+def test_cifar_models_select_the_cifar_input_through_the_cli_flags():
+    from azure_hc_intel_tf_b200.utils import flags
+    p = flags.parse(["--model=resnet56", "--batch_size=8", "--variable_update=horovod", "--device=cpu"])
+    assert p.data_name == "cifar10" and any("cifar10" in n for n in p.notes)
+    p = flags.parse(["--model=resnet50", "--batch_size=8", "--variable_update=horovod", "--device=cpu"])
+    assert p.data_name == "imagenet"
+
+
+def test_tf_variable_names_of_the_preactivation_models():
+    """ResNet v2 / DenseNet use standalone batch-norms; their scopes follow the builder's counters like the conv ones."""
+    m = create_model("resnet20_v2")
+    names = {getattr(p, "tf_name", None) for p in m.parameters()}
+    assert "v0/cg/conv0/conv2d/kernel" in names
+    assert any(n and n.startswith("v0/cg/resnet_v20/batchnorm") and n.endswith("/gamma") for n in names)
+    assert "v0/cg/affine0/weights" in names
+    assert None not in names
 
 
 def test_registry_and_unknown_model():
