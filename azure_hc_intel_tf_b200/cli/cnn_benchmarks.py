@@ -217,8 +217,11 @@ class BenchmarkCNN:
         self._sync()
         self._barrier()
         self._sync()
-        if p.trace_file and self.rank == 0:
-            self._write_trace(p.trace_file)
+        # the profiled step is a real training step with its collectives, so EVERY rank runs it; rank 0 writes
+        if p.graph_file and self.rank == 0:
+            self._write_graph(p.graph_file)
+        if p.trace_file or p.tfprof_file:
+            self._write_trace(p.trace_file, p.tfprof_file)
         if self.rank == 0:
             print("Done warm up")
             print(log.table_header())
@@ -274,9 +277,15 @@ class BenchmarkCNN:
             self.timeline.close()
         return summary
 
-    def _write_trace(self, path: str):
-        """--trace_file: Chrome trace of one training step (tf_cnn_benchmarks' flag of the same name; the reference
-        does not set it — SURVEY.md §5.1). CPU ops, CUDA kernels and NVTX ranges of exactly one step."""
+    def _write_trace(self, trace_path: Optional[str], tfprof_path: Optional[str]):
+        """--trace_file: Chrome trace of one training step; --tfprof_file: per-op time table of the same step
+        (tf_cnn_benchmarks' flags of the same names; the reference sets neither — SURVEY.md §5.1). CPU ops, CUDA
+        kernels and NVTX ranges of exactly one step. Called on every rank (the step contains collectives); only
+        rank 0 profiles and writes."""
+        if self.rank != 0:
+            self.step()
+            self._sync()
+            return
         from torch.profiler import ProfilerActivity, profile
         acts = [ProfilerActivity.CPU] + ([ProfilerActivity.CUDA] if self.device.type == "cuda" else [])
         was = self._nvtx
@@ -285,8 +294,44 @@ class BenchmarkCNN:
             self.step()
             self._sync()
         self._nvtx = was
-        prof.export_chrome_trace(path)
-        print(f"Wrote trace of one step to {path}")
+        if trace_path:
+            prof.export_chrome_trace(trace_path)
+            print(f"Wrote trace of one step to {trace_path}")
+        if tfprof_path:
+            key = "device_time_total" if self.device.type == "cuda" else "self_cpu_time_total"
+            evs = sorted(prof.key_averages(), key=lambda e: -getattr(e, key, 0.0))
+            with open(tfprof_path, "w") as f:
+                f.write(f"# per-op profile of one training step: model={self.model.name} batch={self.batch} "
+                        f"device={self.device.type}; times in microseconds, sorted by {key}\n")
+                f.write(f"{'calls':>7s} {'device_us':>12s} {'self_cpu_us':>12s}  op\n")
+                for e in evs:
+                    dev_us = float(getattr(e, "device_time_total", 0.0) or 0.0)
+                    cpu_us = float(getattr(e, "self_cpu_time_total", 0.0) or 0.0)
+                    if dev_us <= 0.0 and cpu_us <= 0.0:
+                        continue
+                    f.write(f"{e.count:7d} {dev_us:12.1f} {cpu_us:12.1f}  {e.key}\n")
+            print(f"Wrote per-op profile of one step to {tfprof_path}")
+
+    def _write_graph(self, path: str):
+        """--graph_file: a text description of the model graph (tf_cnn_benchmarks writes the GraphDef; here: one line
+        per layer in module order with its geometry, then every variable with its tf_cnn_benchmarks name, checkpoint
+        layout and shape)."""
+        with open(path, "w") as f:
+            f.write(f"# model {self.model.name}: input {self.model.image_size}x{self.model.image_size}x3, "
+                    f"{self.model.cfg.num_classes} classes, kernels={self.kernels}\n# layers\n")
+            for name, mod in self.model.named_modules():
+                if len(list(mod.children())) == 0:
+                    f.write(f"{name or '.'}: {mod.__class__.__name__}({mod.extra_repr()})\n")
+            f.write("# variables (tf name, layout, shape, trainable)\n")
+            total = 0
+            for pname, prm in self.model.named_parameters():
+                if getattr(prm, "tf_skip", False):
+                    continue
+                total += prm.numel() if prm.requires_grad else 0
+                f.write(f"{getattr(prm, 'tf_name', pname)} {getattr(prm, 'tf_layout', '-')} {tuple(prm.shape)} "
+                        f"{'trainable' if prm.requires_grad else 'frozen'}\n")
+            f.write(f"# trainable parameters: {total}\n")
+        print(f"Wrote model graph description to {path}")
 
     def _maybe_save(self):
         p = self.p

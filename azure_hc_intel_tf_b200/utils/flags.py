@@ -75,6 +75,8 @@ class Params:
     save_model_steps: int = 0
     save_model_secs: int = 0
     trace_file: Optional[str] = None
+    tfprof_file: Optional[str] = None
+    graph_file: Optional[str] = None
     print_training_accuracy: bool = False
     seed: int = 1234
     # --- B200 additions
@@ -122,6 +124,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--save_model_steps", type=int, default=0)
     p.add_argument("--save_model_secs", type=int, default=0)
     p.add_argument("--trace_file", type=str, default=None)
+    p.add_argument("--tfprof_file", type=str, default=None)
+    p.add_argument("--graph_file", type=str, default=None)
     p.add_argument("--print_training_accuracy", type=absl_bool, default=False, nargs="?", const=True)
     p.add_argument("--seed", type=int, default=d.seed)
     p.add_argument("--fabric", type=str, default=d.fabric, choices=FABRICS)

@@ -37,3 +37,22 @@ def test_cli_resnet50_batch32_ws2_cpu():
             "--variable_update=horovod", "--display_every=1", "--optimizer=momentum"]
     outs = testing.run_ranks(W.w_cli, 2, "gloo", args=(argv,), timeout=900)
     assert outs[0][0] > 0 and abs(outs[0][1] - outs[1][1]) < 1e-3     # same weights on both ranks
+
+
+def test_trace_graph_and_tfprof_files_ws2_cpu(tmp_path):
+    """--trace_file / --tfprof_file / --graph_file (tf_cnn_benchmarks hooks the reference leaves unset).
+    The profiled step is a real training step with its allreduce, so every rank must run it (with only rank 0
+    stepping, the ranks' collective counts diverge and the run hangs); rank 0 writes the files."""
+    import json
+    trace, prof, graph = tmp_path / "trace.json", tmp_path / "tfprof.txt", tmp_path / "graph.txt"
+    argv = ["--model=lenet", "--batch_size=4", "--num_batches=2", "--num_warmup_batches=1", "--device=cpu",
+            "--variable_update=horovod", "--display_every=1", f"--trace_file={trace}", f"--tfprof_file={prof}",
+            f"--graph_file={graph}"]
+    outs = testing.run_ranks(W.w_cli, 2, "gloo", args=(argv,), timeout=600)
+    assert abs(outs[0][1] - outs[1][1]) < 1e-4              # ranks still in lock-step after the extra profiled step
+    assert "traceEvents" in json.load(open(trace))
+    text = open(prof).read()
+    assert text.startswith("# per-op profile of one training step: model=lenet") and len(text.splitlines()) > 5
+    g = open(graph).read()
+    assert "v0/cg/conv0/conv2d/kernel HWIO (32, 3, 5, 5) trainable" in g and "v0/cg/affine1/weights IO" in g
+    assert "# trainable parameters:" in g
