@@ -19,7 +19,7 @@ import torch
 
 from .. import hvd, models, ops
 from ..ops import data as data_mod
-from ..utils import ckpt, flags as flags_mod, log
+from ..utils import ckpt, flags as flags_mod, log, lr_schedule
 from ..utils.timeline import Timeline
 
 
@@ -57,7 +57,14 @@ class BenchmarkCNN:
         self.model.train(not p.forward_only)
         self.warmup = p.num_warmup_batches if p.num_warmup_batches is not None else max(10, min(50, p.num_batches))
         self.lr = p.init_learning_rate if p.init_learning_rate is not None else self.model.get_learning_rate(self.global_batch)
-        self.timeline = Timeline(p.timeline, self.rank) if p.timeline else None
+        # --timeline=<file>, or Horovod's own switch HOROVOD_TIMELINE=<file> that the reference's launcher would
+        # forward to every rank with -x (run-tf-sing-ucx-openmpi.sh:104-106)
+        tl_path = p.timeline or p.horovod_timeline
+        self.timeline = Timeline(tl_path, self.rank) if tl_path else None
+        # whole-step CUDA graph: on by default for the sm_100a kernel path (the configuration bench.py measures); a
+        # timeline needs per-bucket events, which a replayed graph cannot give, so it switches the graph off
+        self.use_graph = (p.use_cuda_graph if p.use_cuda_graph is not None else
+                          (self.kernels == "b200" and want_cuda and self.timeline is None and not p.forward_only))
         self.opt = None if p.forward_only else self._make_optimizer()
         self.global_step = 0
         if p.train_dir:
@@ -81,13 +88,17 @@ class BenchmarkCNN:
     def _make_optimizer(self):
         p = self.p
         named = [(n, q) for n, q in self.model.named_parameters() if q.requires_grad]
-        thr = flags_mod.resolve_fusion_threshold(p)
+        thr = flags_mod.resolve_fusion_threshold(p, self.fabric if self.world > 1 else None)
         native = p.optimizer in ("momentum", "sgd", "lars") and not (self.kernels == "cudnn" and self.fabric == "nccl")
         if native:
             mu = 0.0 if p.optimizer == "sgd" else p.momentum
             opt = hvd.MomentumSGD(named, lr=self.lr, momentum=mu, weight_decay=p.weight_decay,
                                   lars=p.optimizer == "lars", lars_eta=p.lars_eta,
                                   lowp=self.kernels == "b200", fusion_threshold=thr)
+            if p.lr_schedule != "constant" or p.num_learning_rate_warmup_epochs > 0:
+                n_img = 50000 if p.data_name == "cifar10" else lr_schedule.IMAGENET_TRAIN
+                opt.lr_schedule = lr_schedule.make(p.lr_schedule, self.lr, self.global_batch,
+                                                   p.num_learning_rate_warmup_epochs, p.num_epochs_total, n_img)
         else:
             # stock-library baseline (and rmsprop / adam): torch.optim on the fp32 parameters
             ps = [q for _, q in named]
@@ -137,7 +148,7 @@ class BenchmarkCNN:
 
     def step(self):
         images, labels = self.data.next()
-        if self.p.use_cuda_graph and self.device.type == "cuda":
+        if self.use_graph and self.device.type == "cuda":
             return self._graph_step(images, labels)
         return self.train_step(images, labels)
 
@@ -145,8 +156,12 @@ class BenchmarkCNN:
     def _graph_step(self, images, labels):
         """Replay the captured step (forward, backward, fused gradient exchange and update: every launch of the
         step, including the side-stream collectives) with this step's batch. The first call runs three eager steps
-        (lazy initialisation, plan handshake, allocator warm-up) and then captures. Learning rate and other launch
-        scalars are baked into the graph; changing them needs a re-capture (``self._graph = None``)."""
+        (lazy initialisation, plan handshake, allocator warm-up) and then captures. The learning rate is a device
+        scalar the update kernels read at run time, so a schedule keeps working across replays; momentum and weight
+        decay are launch scalars baked into the graph (changing them needs a re-capture: ``self._graph = None``)."""
+        opt = getattr(self.opt, "_opt", self.opt)
+        if self._graph is not None and hasattr(opt, "apply_schedule"):
+            opt.apply_schedule()          # host → device scalar, ordered before the replay on this stream
         if self._graph is None:
             self._g_images = images.clone(memory_format=torch.preserve_format)
             self._g_labels = labels.clone()
@@ -166,6 +181,8 @@ class BenchmarkCNN:
             self._g_labels.copy_(labels, non_blocking=True)
         self._graph.replay()
         self.global_step += 1
+        if hasattr(opt, "lr_dev"):
+            opt.steps += 1                # the captured step() ran on the device only; keep the schedule's clock going
         return self._g_loss
 
     # ------------------------------------------------------------------ reporting

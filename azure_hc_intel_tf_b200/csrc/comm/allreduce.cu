@@ -1,8 +1,9 @@
-// allreduce.cu — allreduce (+ fused 1/N scale and momentum-SGD update), broadcast and barrier over NVLink peer
-// memory. See include/b200comm.h for the contract and the reference citations (Horovod's MPI_Allreduce over
-// OpenMPI/UCX or Intel MPI/libfabric, followed by TF ApplyMomentum).
+// allreduce.cu — allreduce (+ fused 1/N scale and momentum-SGD / LARS update), all-gather, broadcast, barrier and
+// point-to-point probes over NVLink peer memory. See include/b200comm.h for the contract and the reference citations
+// (Horovod's MPI_Allreduce over OpenMPI/UCX or Intel MPI/libfabric, followed by TF ApplyMomentum; the OSU
+// micro-benchmark roles).
 //
-// Algorithm (two-shot, per 1024-element block b of the message, owner(b) = b mod world):
+// Algorithm (two-shot, per 512-element block b of the message, owner(b) = b mod world):
 //   barrier                      every rank's gradients for this bucket are complete and visible
 //   owner: acc = sum_p peer_p[b]  in rank order (peer loads over NVLink), acc *= scale
 //          peer_p[b] = acc        for every p (peer stores): the all-gather
@@ -12,15 +13,39 @@
 // Cross-GPU barriers are per CTA: CTA c of every rank exchanges an epoch number with CTA c of every other rank
 // through st.release.sys / ld.acquire.sys on flag words in the peers' signal pads. Epochs live in device memory and
 // only ever grow, so nothing is reset between calls and a captured CUDA graph can be replayed.
+//
+// What a per-CTA barrier proves, and what the code after it may therefore touch: when CTA c passes the second
+// barrier it knows that CTA c of every rank has finished its reduce + all-gather, i.e. that the blocks
+// { j * world + p : j = c, c + G, c + 2G, ... ; p = 0 .. world-1 } (G = gridDim.x) hold their final value in this
+// rank's buffer. It knows nothing about blocks written by OTHER CTA indices of other ranks. The fused momentum-SGD
+// half therefore walks exactly that block set. The LARS variant needs whole-tensor norms, so it first joins all
+// CTAs of this rank with a device-local grid barrier (every CTA has then passed its cross-rank barrier, so every
+// block is final) and only then reads across blocks.
+//
+// All kernels of this file that use the signal pad must be ordered on ONE stream per device (they share the per-CTA
+// epoch slots); parallel/symm.py serialises them on the context's communication stream.
 #include "b200comm.h"
 #include "common.cuh"
 
 namespace b200 {
 namespace {
 
-constexpr int kThreads = 256;
+// 128 threads x one 16-byte vector = one 512-element block. Small CTAs on purpose: a convolution CTA (576 threads x 96
+// registers, <= 223 KiB shared memory) leaves 10,240 registers and a few KiB of shared memory free on its SM, and a
+// 128-thread CTA of these kernels (<= 80 registers, a few bytes of shared memory) fits into that gap, so a collective
+// launched on the side stream makes progress WHILE a persistent convolution kernel holds every SM.
+constexpr int kThreads = 128;
+constexpr int kBlock = kThreads * 4;          // fp32 elements per block
+constexpr int kBlockBf16 = kThreads * 8;      // bf16 elements per block
 constexpr int kPadFlagWords = B200_COMM_MAX_CTAS * B200_COMM_MAX_RANKS;   // written by peers
-constexpr int kPadWords = kPadFlagWords + B200_COMM_MAX_CTAS;             // + per-CTA epoch counters (local)
+constexpr int kPadEpochWords = B200_COMM_MAX_CTAS;                        // per-CTA epoch counters (local)
+// local grid barrier (count, generation), then the point-to-point probe's mailboxes: per partner rank one flag word
+// (written by that partner) and one local message count, so exchanges with different partners do not interfere
+constexpr int kPadGridCnt = kPadFlagWords + kPadEpochWords;
+constexpr int kPadGridGen = kPadGridCnt + 1;
+constexpr int kPadP2PFlag = kPadGridCnt + 2;                              // one word per sending rank
+constexpr int kPadP2PSeq = kPadP2PFlag + B200_COMM_MAX_RANKS;             // one word per partner rank
+constexpr int kPadWords = kPadP2PSeq + B200_COMM_MAX_RANKS + 2;
 
 struct CommDev {
   uint64_t buf[B200_COMM_MAX_RANKS];
@@ -34,6 +59,8 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+
+constexpr uint64_t kWatchdogNs = 30000000000ull;   // 30 s: a peer never arrived; fail loudly instead of hanging
 
 // All threads of the CTA call this. s_epoch is a shared-memory word holding this CTA's last used epoch.
 __device__ __forceinline__ void cta_barrier_all_ranks(const CommDev& c, uint32_t* s_epoch) {
@@ -50,7 +77,7 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const CommDev& c, uint32_t
     for (;;) {
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src) : "memory");
       if ((int32_t)(v - e) >= 0) break;
-      if (globaltimer_ns() - t0 > 30000000000ull) {   // 30 s: a peer never arrived; fail loudly instead of hanging
+      if (globaltimer_ns() - t0 > kWatchdogNs) {
         printf("b200 comm: rank %d CTA %d timed out waiting for rank %d (epoch %u, saw %u)\n", c.rank, blockIdx.x, t, e, v);
         __trap();
       }
@@ -65,6 +92,36 @@ __device__ __forceinline__ uint32_t* epoch_slot(const CommDev& c) {
   return reinterpret_cast<uint32_t*>(c.pad[c.rank]) + kPadFlagWords + blockIdx.x;
 }
 
+// Join all CTAs of THIS rank's launch (they are co-resident: each of them spins on peer flags anyway). Sense
+// reversal on a generation word: every CTA reads the generation before it arrives, the last arriver resets the count
+// and bumps the generation. Works for any grid size per launch because the count returns to zero.
+__device__ __forceinline__ void grid_barrier_local(const CommDev& c) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(c.pad[c.rank]) + kPadGridCnt;
+    uint32_t* gen = reinterpret_cast<uint32_t*>(c.pad[c.rank]) + kPadGridGen;
+    __threadfence();
+    uint32_t g;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(gen) : "memory");
+    if (atomicAdd(cnt, 1u) == gridDim.x - 1) {
+      *cnt = 0;
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(gen), "r"(g + 1) : "memory");
+    } else {
+      uint32_t v;
+      const uint64_t t0 = globaltimer_ns();
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gen) : "memory");
+        if (globaltimer_ns() - t0 > kWatchdogNs) {
+          printf("b200 comm: rank %d CTA %d timed out in the local grid barrier\n", c.rank, blockIdx.x);
+          __trap();
+        }
+      } while (v == g);
+    }
+  }
+  __syncthreads();
+}
+
 struct SgdDev {
   float* master;
   float* mom;
@@ -72,22 +129,91 @@ struct SgdDev {
   const int32_t* block_tensor;
   const float* tdecay;
   const float* tlars;
-  const float* trust;
+  float* trust;
+  const float* lr_dev;      // when non-null the learning rate is read from device memory (schedules under a CUDA graph)
   float lr, mu, wd;
   int enabled;
+  // LARS (fused): per-block (kBlock elements) partial norms, per-tensor block ranges, the tensors that END in this bucket and the
+  // block range [upd_lo, upd_hi) they span (it may start in an earlier bucket when a tensor was split)
+  float* block_partials;
+  const int32_t* tblk_lo;
+  const int32_t* tblk_cnt;
+  int t_lo, t_hi;
+  int64_t upd_lo, upd_hi;
+  float eta, eps;
 };
 
+// Peer (and post-barrier local) data must not come from a stale L1 line: a relaxed load at system scope is a strong
+// operation (served from the point of coherence, never from this SM's non-coherent L1), and no_allocate keeps it from
+// leaving a line behind.
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
-  // peer (and post-barrier local) data must not come from a stale L1 line
   float4 v;
-  asm volatile("ld.global.cv.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
   return v;
 }
 
-template <bool kNvls>
+__device__ __forceinline__ void st_peer_f4(float* p, const float4& v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void sgd_apply_block(const SgdDev& sgd, const float4 gv, int64_t gb, int tid, float lr) {
+  float dec = sgd.wd, tr = 1.0f;
+  if (sgd.block_tensor) {
+    const int t = sgd.block_tensor[(gb * kBlock) >> 10];   // the table has one entry per 1024 elements
+    if (t < 0) return;                         // padding between tensors stays untouched
+    dec = sgd.wd * sgd.tdecay[t];
+    if (sgd.trust && sgd.tlars[t] != 0.0f) tr = sgd.trust[t];
+  }
+  const int64_t i = gb * kBlock + tid * 4;
+  const float4 wv = *reinterpret_cast<const float4*>(sgd.master + i);
+  const float4 mv = *reinterpret_cast<const float4*>(sgd.mom + i);
+  float ww[4] = {wv.x, wv.y, wv.z, wv.w}, mm[4] = {mv.x, mv.y, mv.z, mv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float ge = (gg[k] + dec * ww[k]) * tr;
+    mm[k] = sgd.mu * mm[k] + ge;
+    ww[k] -= lr * mm[k];
+  }
+  *reinterpret_cast<float4*>(sgd.master + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+  *reinterpret_cast<float4*>(sgd.mom + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+  if (sgd.shadow) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(sgd.shadow + i) = pk;
+  }
+}
+
+// Sum over the CTA of two per-thread values, in a fixed order (warp tree, then warps 0..7 in sequence).
+__device__ __forceinline__ float2 cta_sum2(float a, float b, float (*red)[8]) {
+  a = warp_sum(a);
+  b = warp_sum(b);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) {
+    red[0][warp] = a;
+    red[1][warp] = b;
+  }
+  __syncthreads();
+  float sa = 0.0f, sb = 0.0f;
+#pragma unroll
+  for (int k = 0; k < kThreads / 32; ++k) {
+    sa += red[0][k];
+    sb += red[1][k];
+  }
+  return make_float2(sa, sb);
+}
+
+template <bool kNvls, bool kLars>
 __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int64_t offset, int64_t nblk, float scale,
                                                                  SgdDev sgd) {
   __shared__ uint32_t s_epoch;
+  __shared__ float s_red[2][8];
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
   __syncthreads();
   cta_barrier_all_ranks(c, &s_epoch);
@@ -97,7 +223,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
   for (int64_t j = blockIdx.x;; j += gridDim.x) {
     const int64_t b = j * c.world + c.rank;
     if (b >= nblk) break;
-    const int64_t off = offset + b * 1024 + tid * 4;
+    const int64_t off = offset + b * kBlock + tid * 4;
     if (kNvls) {
       // NVLS: one load returns the sum over all ranks' copies, computed inside the NVSwitch; one store lands in
       // every rank's copy. Link traffic per GPU: S/N reduced in + S/N out, instead of (N-1)/N*S each way.
@@ -107,7 +233,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
-        mp[u] = bu < nblk ? reinterpret_cast<float*>(c.mc) + offset + bu * 1024 + tid * 4 : nullptr;
+        mp[u] = bu < nblk ? reinterpret_cast<float*>(c.mc) + offset + bu * kBlock + tid * 4 : nullptr;
         if (mp[u])
           asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
                        : "=f"(acc[u].x), "=f"(acc[u].y), "=f"(acc[u].z), "=f"(acc[u].w)
@@ -143,117 +269,120 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
     acc.w *= scale;
 #pragma unroll
     for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.buf[p]) + off) = acc;
+      if (p < c.world) st_peer_f4(reinterpret_cast<float*>(c.buf[p]) + off, acc);
   }
   cta_barrier_all_ranks(c, &s_epoch);
 
   // ---- fused optimizer half: every rank updates its replica from the (now identical) reduced gradient
   if (sgd.enabled) {
     const float* g = reinterpret_cast<const float*>(c.buf[c.rank]);
-    for (int64_t b = blockIdx.x; b < nblk; b += gridDim.x) {
-      const int64_t gb = offset / 1024 + b;          // global 1024-block index
-      float dec = sgd.wd, tr = 1.0f;
-      if (sgd.block_tensor) {
-        const int t = sgd.block_tensor[gb];
-        if (t < 0) continue;
-        dec = sgd.wd * sgd.tdecay[t];
-        if (sgd.trust && sgd.tlars[t] != 0.0f) tr = sgd.trust[t];
-      }
-      const int64_t i = gb * 1024 + tid * 4;
-      const float4 gv = ld_peer_f4(g + i);
-      float4 wv = *reinterpret_cast<const float4*>(sgd.master + i);
-      float4 mv = *reinterpret_cast<const float4*>(sgd.mom + i);
-      float ww[4] = {wv.x, wv.y, wv.z, wv.w}, mm[4] = {mv.x, mv.y, mv.z, mv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+    const float lr = sgd.lr_dev ? __ldg(sgd.lr_dev) : sgd.lr;
+    if (!kLars) {
+      // exactly the blocks this CTA's barrier covers: j in {blockIdx.x + k*gridDim.x}, all owners p of that j
+      for (int64_t j = blockIdx.x; j * c.world < nblk; j += gridDim.x) {
+        float4 gv[B200_COMM_MAX_RANKS];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float ge = (gg[k] + dec * ww[k]) * tr;
-        mm[k] = sgd.mu * mm[k] + ge;
-        ww[k] -= sgd.lr * mm[k];
+        for (int p = 0; p < B200_COMM_MAX_RANKS; ++p) {
+          const int64_t b = j * c.world + p;
+          if (p < c.world && b < nblk) gv[p] = ld_peer_f4(g + offset + b * kBlock + tid * 4);
+        }
+#pragma unroll
+        for (int p = 0; p < B200_COMM_MAX_RANKS; ++p) {
+          const int64_t b = j * c.world + p;
+          if (p < c.world && b < nblk) sgd_apply_block(sgd, gv[p], offset / kBlock + b, tid, lr);
+        }
       }
-      *reinterpret_cast<float4*>(sgd.master + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
-      *reinterpret_cast<float4*>(sgd.mom + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-      if (sgd.shadow) {
-        __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
-        uint2 pk;
-        pk.x = *reinterpret_cast<uint32_t*>(&lo);
-        pk.y = *reinterpret_cast<uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(sgd.shadow + i) = pk;
+    } else {
+      // (1) per-block partial norms of this bucket's blocks (any CTA may take any block after the grid barrier...
+      //     but the partials are cheap, so they are taken right here for the covered set, then everyone joins)
+      for (int64_t j = blockIdx.x; j * c.world < nblk; j += gridDim.x) {
+        for (int p = 0; p < c.world; ++p) {
+          const int64_t b = j * c.world + p;
+          if (b >= nblk) break;
+          const int64_t gb = offset / kBlock + b;
+          const int64_t i = gb * kBlock + tid * 4;
+          const float4 gv = ld_peer_f4(g + i);
+          const float4 wv = *reinterpret_cast<const float4*>(sgd.master + i);
+          const float2 s = cta_sum2(wv.x * wv.x + wv.y * wv.y + wv.z * wv.z + wv.w * wv.w,
+                                    gv.x * gv.x + gv.y * gv.y + gv.z * gv.z + gv.w * gv.w, s_red);
+          if (tid == 0) {
+            sgd.block_partials[2 * gb] = s.x;
+            sgd.block_partials[2 * gb + 1] = s.y;
+          }
+        }
       }
+      grid_barrier_local(c);
+      // (2) trust ratio of every tensor that ends in this bucket: its blocks' partials folded in a fixed order
+      for (int t = sgd.t_lo + blockIdx.x; t < sgd.t_hi; t += gridDim.x) {
+        const int lo = sgd.tblk_lo[t], cnt = sgd.tblk_cnt[t];
+        float sw = 0.0f, sg = 0.0f;
+        for (int b = tid; b < cnt; b += kThreads) {
+          sw += __ldcg(sgd.block_partials + 2 * (lo + b));
+          sg += __ldcg(sgd.block_partials + 2 * (lo + b) + 1);
+        }
+        const float2 s = cta_sum2(sw, sg, s_red);
+        if (tid == 0) {
+          float r = 1.0f;
+          if (sgd.tlars[t] != 0.0f) {
+            const float wn = sqrtf(s.x), gn = sqrtf(s.y);
+            if (wn > 0.0f && gn > 0.0f) r = sgd.eta * wn / (gn + sgd.wd * sgd.tdecay[t] * wn + sgd.eps);
+          }
+          sgd.trust[t] = r;
+        }
+      }
+      grid_barrier_local(c);
+      // (3) update the blocks of those tensors (the range may reach back into an earlier bucket)
+      for (int64_t gb = sgd.upd_lo + blockIdx.x; gb < sgd.upd_hi; gb += gridDim.x)
+        sgd_apply_block(sgd, ld_peer_f4(g + gb * kBlock + tid * 4), gb, tid, lr);
     }
   }
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
 }
 
-// One-shot variant for small messages (one 1024-element block per CTA): every rank reads the block from all peers and
+// One-shot variant for small messages (one block per CTA): every rank reads the block from all peers and
 // reduces it itself in rank order - a single NVLink traversal instead of two. The second barrier keeps a fast rank
-// from overwriting its buffer while a slower peer is still reading it.
-__global__ void __launch_bounds__(kThreads) allreduce_f32_oneshot_kernel(CommDev c, int64_t offset, int64_t nblk,
+// from overwriting its buffer while a slower peer is still reading it. n only has to be a multiple of 4 elements
+// here (the tail block is masked), which is what lets the sweep go below 4 KiB without padding in the tool.
+__global__ void __launch_bounds__(kThreads) allreduce_f32_oneshot_kernel(CommDev c, int64_t offset, int64_t n,
                                                                          float scale, SgdDev sgd) {
   __shared__ uint32_t s_epoch;
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
   __syncthreads();
   cta_barrier_all_ranks(c, &s_epoch);
   const int tid = threadIdx.x;
-  const int64_t b = blockIdx.x;              // grid == nblk
-  const int64_t off = offset + b * 1024 + tid * 4;
+  const int64_t b = blockIdx.x;              // grid == number of blocks
+  const int64_t off = offset + b * kBlock + tid * 4;
+  const bool live = b * kBlock + tid * 4 < n;
   float4 v[B200_COMM_MAX_RANKS];
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (live) {
 #pragma unroll
-  for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-    if (p < c.world) v[p] = ld_peer_f4(reinterpret_cast<const float*>(c.buf[p]) + off);
-  float4 acc = v[0];
+    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
+      if (p < c.world) v[p] = ld_peer_f4(reinterpret_cast<const float*>(c.buf[p]) + off);
+    acc = v[0];
 #pragma unroll
-  for (int p = 1; p < B200_COMM_MAX_RANKS; ++p)
-    if (p < c.world) {
-      acc.x += v[p].x;
-      acc.y += v[p].y;
-      acc.z += v[p].z;
-      acc.w += v[p].w;
-    }
-  acc.x *= scale;
-  acc.y *= scale;
-  acc.z *= scale;
-  acc.w *= scale;
+    for (int p = 1; p < B200_COMM_MAX_RANKS; ++p)
+      if (p < c.world) {
+        acc.x += v[p].x;
+        acc.y += v[p].y;
+        acc.z += v[p].z;
+        acc.w += v[p].w;
+      }
+    acc.x *= scale;
+    acc.y *= scale;
+    acc.z *= scale;
+    acc.w *= scale;
+  }
   cta_barrier_all_ranks(c, &s_epoch);
-  *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.buf[c.rank]) + off) = acc;
-  if (sgd.enabled) {
-    const int64_t gb = offset / 1024 + b;
-    float dec = sgd.wd, tr = 1.0f;
-    bool skip = false;
-    if (sgd.block_tensor) {
-      const int t = sgd.block_tensor[gb];
-      if (t < 0) {
-        skip = true;
-      } else {
-        dec = sgd.wd * sgd.tdecay[t];
-        if (sgd.trust && sgd.tlars[t] != 0.0f) tr = sgd.trust[t];
-      }
-    }
-    if (!skip) {
-      const int64_t i = gb * 1024 + tid * 4;
-      float4 wv = *reinterpret_cast<const float4*>(sgd.master + i);
-      float4 mv = *reinterpret_cast<const float4*>(sgd.mom + i);
-      float ww[4] = {wv.x, wv.y, wv.z, wv.w}, mm[4] = {mv.x, mv.y, mv.z, mv.w}, gg[4] = {acc.x, acc.y, acc.z, acc.w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float ge = (gg[k] + dec * ww[k]) * tr;
-        mm[k] = sgd.mu * mm[k] + ge;
-        ww[k] -= sgd.lr * mm[k];
-      }
-      *reinterpret_cast<float4*>(sgd.master + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
-      *reinterpret_cast<float4*>(sgd.mom + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-      if (sgd.shadow) {
-        __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
-        uint2 pk;
-        pk.x = *reinterpret_cast<uint32_t*>(&lo);
-        pk.y = *reinterpret_cast<uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(sgd.shadow + i) = pk;
-      }
-    }
+  if (live) *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.buf[c.rank]) + off) = acc;
+  if (sgd.enabled && live) {
+    const float lr = sgd.lr_dev ? __ldg(sgd.lr_dev) : sgd.lr;
+    sgd_apply_block(sgd, acc, offset / kBlock + b, tid, lr);
   }
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
 }
 
-// bf16 payload: 2048 elements per block (256 threads x 8), fp32 accumulation, one rounding.
+// bf16 payload: 1024 elements per block (128 threads x 8), fp32 accumulation, one rounding.
 __global__ void __launch_bounds__(kThreads) allreduce_bf16_kernel(CommDev c, int64_t offset, int64_t nblk, float scale) {
   __shared__ uint32_t s_epoch;
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
@@ -263,7 +392,7 @@ __global__ void __launch_bounds__(kThreads) allreduce_bf16_kernel(CommDev c, int
   for (int64_t j = blockIdx.x;; j += gridDim.x) {
     const int64_t b = j * c.world + c.rank;
     if (b >= nblk) break;
-    const int64_t off = offset + b * 2048 + tid * 8;
+    const int64_t off = offset + b * kBlockBf16 + tid * 8;
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
@@ -301,22 +430,131 @@ __global__ void __launch_bounds__(kThreads) barrier_kernel(CommDev c) {
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
 }
 
+// Copy 16-byte vectors [0, nvec) of `src` to the same offset of every peer's buffer (or of the multicast mapping, one
+// store for all of them). `skip` = a rank that needs no copy (the source's own buffer), -1 = none.
+__device__ __forceinline__ void push_to_peers(const CommDev& c, const float* src, int64_t offset, int64_t nvec) {
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) v[u] = *reinterpret_cast<const float4*>(src + (i + u * stride) * 4);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t e = i + u * stride;
+      if (e >= nvec) continue;
+      if (c.mc) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(
+                         reinterpret_cast<float*>(c.mc) + offset + e * 4),
+                     "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w)
+                     : "memory");
+      } else {
+#pragma unroll
+        for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
+          if (p < c.world && p != c.rank) st_peer_f4(reinterpret_cast<float*>(c.buf[p]) + offset + e * 4, v[u]);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(kThreads) broadcast_f32_kernel(CommDev c, int64_t offset, int64_t nvec, int root) {
   __shared__ uint32_t s_epoch;
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
   __syncthreads();
   cta_barrier_all_ranks(c, &s_epoch);     // peers are done with whatever they were doing to these buffers
-  if (c.rank == root) {
-    const float* src = reinterpret_cast<const float*>(c.buf[root]) + offset;
-    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * kThreads) {
-      const float4 v = *reinterpret_cast<const float4*>(src + i * 4);
-#pragma unroll
-      for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-        if (p < c.world && p != root) *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.buf[p]) + offset + i * 4) = v;
-    }
-  }
+  if (c.rank == root) push_to_peers(c, reinterpret_cast<const float*>(c.buf[root]) + offset, offset, nvec);
   cta_barrier_all_ranks(c, &s_epoch);
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
+}
+
+// All-gather: rank r's segment [offset + r*n, +n) of its own buffer is written to the same place in every peer.
+__global__ void __launch_bounds__(kThreads) allgather_f32_kernel(CommDev c, int64_t offset, int64_t nvec_per_rank) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
+  __syncthreads();
+  cta_barrier_all_ranks(c, &s_epoch);
+  const int64_t seg = offset + (int64_t)c.rank * nvec_per_rank * 4;
+  push_to_peers(c, reinterpret_cast<const float*>(c.buf[c.rank]) + seg, seg, nvec_per_rank);
+  cta_barrier_all_ranks(c, &s_epoch);
+  if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
+}
+
+// Point-to-point bandwidth probe (osu_bw / osu_bibw roles): this rank stores (or loads) nvec 16-byte vectors to
+// (from) ONE peer. No barrier inside: the caller brackets it with events; run it on one rank for one direction, on
+// both ranks of a pair for the bidirectional figure.
+__global__ void __launch_bounds__(kThreads) p2p_copy_kernel(CommDev c, int peer, int64_t offset, int64_t nvec, int pull) {
+  const float* src = reinterpret_cast<const float*>(c.buf[pull ? peer : c.rank]) + offset;
+  float* dst = reinterpret_cast<float*>(c.buf[pull ? c.rank : peer]) + offset;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) v[u] = ld_peer_f4(src + (i + u * stride) * 4);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) st_peer_f4(dst + (i + u * stride) * 4, v[u]);
+  }
+}
+
+// Point-to-point latency probe (osu_latency role): ranks a and b bounce a message of nvec vectors `iters` times;
+// one CTA each, every other rank returns at once. Per bounce: payload stores, fence, flag store (release.sys); the
+// receiver spins on the flag (acquire.sys), reads the payload, and answers. Rank a writes the mean ONE-WAY time in
+// microseconds to out_us[0], measured with %globaltimer on the device.
+__global__ void __launch_bounds__(kThreads) p2p_pingpong_kernel(CommDev c, int a, int b, int64_t offset, int nvec,
+                                                                int iters, float* out_us) {
+  if (c.rank != a && c.rank != b) return;
+  const int peer = c.rank == a ? b : a;
+  uint32_t* my_flag = reinterpret_cast<uint32_t*>(c.pad[c.rank]) + kPadP2PFlag + peer;
+  uint32_t* peer_flag = reinterpret_cast<uint32_t*>(c.pad[peer]) + kPadP2PFlag + c.rank;
+  uint32_t* seq_slot = reinterpret_cast<uint32_t*>(c.pad[c.rank]) + kPadP2PSeq + peer;
+  __shared__ uint32_t s_seq;
+  if (threadIdx.x == 0) s_seq = *seq_slot;
+  __syncthreads();
+  uint32_t seq = s_seq;
+  float* mine = reinterpret_cast<float*>(c.buf[c.rank]) + offset;
+  float* theirs = reinterpret_cast<float*>(c.buf[peer]) + offset;
+  float acc = 0.0f;
+  auto send = [&]() {
+    for (int i = threadIdx.x; i < nvec; i += kThreads) st_peer_f4(theirs + i * 4, make_float4(acc, 1.f, 2.f, 3.f));
+    __threadfence_system();
+    __syncthreads();
+    ++seq;
+    if (threadIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flag), "r"(seq) : "memory");
+  };
+  auto recv = [&]() {
+    if (threadIdx.x == 0) {
+      uint32_t v;
+      const uint64_t t0 = globaltimer_ns();
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flag) : "memory");
+        if (globaltimer_ns() - t0 > kWatchdogNs) {
+          printf("b200 comm: rank %d timed out in the ping-pong probe\n", c.rank);
+          __trap();
+        }
+      } while ((int32_t)(v - (seq + 1)) < 0);
+    }
+    __syncthreads();
+    ++seq;
+    for (int i = threadIdx.x; i < nvec; i += kThreads) acc += ld_peer_f4(mine + i * 4).x;
+  };
+  // both sides count every message (sent or received) in `seq`, so a flag value names one message of the exchange
+  const uint64_t t0 = globaltimer_ns();
+  for (int it = 0; it < iters; ++it) {
+    if (c.rank == a) {
+      send();
+      recv();
+    } else {
+      recv();
+      send();
+    }
+  }
+  const uint64_t t1 = globaltimer_ns();
+  if (threadIdx.x == 0) {
+    *seq_slot = seq;
+    if (acc == -1.2345f) out_us[1] = acc;      // keeps the payload reads alive
+    if (c.rank == a && out_us) out_us[0] = (float)((double)(t1 - t0) / (2.0 * iters) * 1e-3);
+  }
 }
 
 int to_dev(const b200_comm* comm, CommDev& d, int& ctas) {
@@ -336,6 +574,14 @@ int to_dev(const b200_comm* comm, CommDev& d, int& ctas) {
   return 0;
 }
 
+// CTAs for a streaming kernel over `blocks` 2 KiB units: no more than the descriptor allows, no more than one per four
+// units (small messages are latency-bound; more CTAs only add flag traffic), at least one.
+int ctas_for(int64_t blocks, int cap) {
+  int64_t want = (blocks + 3) / 4;
+  if (want < 1) want = 1;
+  return (int)(want < cap ? want : cap);
+}
+
 }  // namespace
 }  // namespace b200
 
@@ -344,6 +590,8 @@ using namespace b200;
 extern "C" {
 
 int64_t b200_comm_pad_bytes(void) { return (int64_t)kPadWords * 4; }
+
+int32_t b200_comm_block_elems(void) { return kBlock; }
 
 int b200_symm_alloc(int64_t bytes, void** dptr) {
   B200_CHECK_ARG(bytes > 0 && dptr, "symm_alloc: bad args");
@@ -384,28 +632,67 @@ int b200_allreduce_f32(const b200_comm* comm, int64_t offset, int64_t n, float s
   CommDev d;
   int ctas;
   if (int e = to_dev(comm, d, ctas)) return e;
-  B200_CHECK_ARG(n > 0 && n % 1024 == 0 && offset >= 0 && offset % 1024 == 0,
-                 "allreduce_f32: offset and n must be multiples of 1024 elements");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int algo = comm->algo;
+  B200_CHECK_ARG(algo >= B200_COMM_ALGO_AUTO && algo <= B200_COMM_ALGO_NVLS, "allreduce_f32: unknown algorithm %d", algo);
+  B200_CHECK_ARG(n > 0 && n % 4 == 0 && offset >= 0 && offset % 4 == 0, "allreduce_f32: offset and n must be multiples of 4 elements");
   SgdDev s{};
+  bool lars = false;
   if (sgd) {
     B200_CHECK_ARG(sgd->master && sgd->mom, "allreduce_f32: fused update needs master and momentum buffers");
     B200_CHECK_ARG(!sgd->block_tensor || sgd->tensor_decay, "allreduce_f32: block table needs tensor_decay");
     B200_CHECK_ARG(!sgd->trust || sgd->tensor_lars, "allreduce_f32: trust needs tensor_lars");
-    s = SgdDev{sgd->master, sgd->mom, sgd->shadow, sgd->block_tensor, sgd->tensor_decay, sgd->tensor_lars, sgd->trust,
-               sgd->lr, sgd->mu, sgd->wd, 1};
+    B200_CHECK_ARG(n % 1024 == 0 && offset % 1024 == 0, "allreduce_f32: the fused update works on whole 1024-element blocks");
+    s.master = sgd->master;
+    s.mom = sgd->mom;
+    s.shadow = sgd->shadow;
+    s.block_tensor = sgd->block_tensor;
+    s.tdecay = sgd->tensor_decay;
+    s.tlars = sgd->tensor_lars;
+    s.trust = sgd->trust;
+    s.lr_dev = sgd->lr_dev;
+    s.lr = sgd->lr;
+    s.mu = sgd->mu;
+    s.wd = sgd->wd;
+    s.enabled = 1;
+    if (sgd->lars_block_partials) {
+      B200_CHECK_ARG(sgd->trust && sgd->block_tensor && sgd->tensor_blk_lo && sgd->tensor_blk_cnt,
+                     "allreduce_f32: fused LARS needs trust, block_tensor and the per-tensor block ranges");
+      B200_CHECK_ARG(sgd->lars_t_lo >= 0 && sgd->lars_t_hi >= sgd->lars_t_lo && sgd->lars_upd_lo >= 0 &&
+                         sgd->lars_upd_hi >= sgd->lars_upd_lo && sgd->lars_upd_hi * kBlock <= offset + n,
+                     "allreduce_f32: fused LARS tensor / block range is inconsistent");
+      lars = true;
+      s.block_partials = sgd->lars_block_partials;
+      s.tblk_lo = sgd->tensor_blk_lo;
+      s.tblk_cnt = sgd->tensor_blk_cnt;
+      s.t_lo = sgd->lars_t_lo;
+      s.t_hi = sgd->lars_t_hi;
+      s.upd_lo = sgd->lars_upd_lo;
+      s.upd_hi = sgd->lars_upd_hi;
+      s.eta = sgd->lars_eta;
+      s.eps = sgd->lars_eps;
+    }
   }
-  const int64_t nblk = n / 1024;
+  const int64_t nblk = (n + kBlock - 1) / kBlock;
   const int64_t one_shot_max = comm->one_shot_max_bytes > 0 ? comm->one_shot_max_bytes : 0;
-  if (n * 4 <= one_shot_max && nblk <= B200_COMM_MAX_CTAS) {
-    allreduce_f32_oneshot_kernel<<<(int)nblk, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
+  const bool one_shot = !lars && nblk <= B200_COMM_MAX_CTAS &&
+                        (algo == B200_COMM_ALGO_ONE_SHOT || (algo == B200_COMM_ALGO_AUTO && n * 4 <= one_shot_max));
+  if (one_shot) {
+    allreduce_f32_oneshot_kernel<<<(int)nblk, kThreads, 0, st>>>(d, offset, n, scale, s);
     B200_LAUNCH_CHECK();
     return 0;
   }
-  if (nblk < ctas) ctas = (int)nblk;
-  if (comm->mc && comm->nvls_min_bytes >= 0 && n * 4 >= comm->nvls_min_bytes && comm->world > 2)
-    allreduce_f32_kernel<true><<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
-  else
-    allreduce_f32_kernel<false><<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale, s);
+  B200_CHECK_ARG(n % 1024 == 0 && offset % 1024 == 0,
+                 "allreduce_f32: beyond the one-shot range offset and n must be multiples of 1024 elements");
+  // each rank owns nblk/world blocks; the NVLS loop takes four per trip
+  ctas = ctas_for((nblk + d.world - 1) / d.world, ctas);
+  bool nvls = comm->mc != 0 && (algo == B200_COMM_ALGO_NVLS ||
+                                (algo == B200_COMM_ALGO_AUTO && comm->nvls_min_bytes >= 0 && n * 4 >= comm->nvls_min_bytes));
+  B200_CHECK_ARG(algo != B200_COMM_ALGO_NVLS || nvls, "allreduce_f32: NVLS requested but the buffer has no multicast mapping");
+  if (nvls && lars) allreduce_f32_kernel<true, true><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
+  else if (nvls) allreduce_f32_kernel<true, false><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
+  else if (lars) allreduce_f32_kernel<false, true><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
+  else allreduce_f32_kernel<false, false><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -416,8 +703,8 @@ int b200_allreduce_bf16(const b200_comm* comm, int64_t offset, int64_t n, float 
   if (int e = to_dev(comm, d, ctas)) return e;
   B200_CHECK_ARG(n > 0 && n % 2048 == 0 && offset >= 0 && offset % 2048 == 0,
                  "allreduce_bf16: offset and n must be multiples of 2048 elements");
-  const int64_t nblk = n / 2048;
-  if (nblk < ctas) ctas = (int)nblk;
+  const int64_t nblk = n / kBlockBf16;
+  ctas = ctas_for((nblk + d.world - 1) / d.world, ctas);
   allreduce_bf16_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale);
   B200_LAUNCH_CHECK();
   return 0;
@@ -438,7 +725,46 @@ int b200_broadcast_f32(const b200_comm* comm, int64_t offset, int64_t n, int32_t
   if (int e = to_dev(comm, d, ctas)) return e;
   B200_CHECK_ARG(n > 0 && n % 4 == 0 && offset >= 0 && offset % 4 == 0 && root >= 0 && root < d.world,
                  "broadcast_f32: n and offset must be multiples of 4, root in range");
+  ctas = ctas_for(n / kBlock, ctas);
   broadcast_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, n / 4, root);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_allgather_f32(const b200_comm* comm, int64_t offset, int64_t n_per_rank, void* stream) {
+  CommDev d;
+  int ctas;
+  if (int e = to_dev(comm, d, ctas)) return e;
+  B200_CHECK_ARG(n_per_rank > 0 && n_per_rank % 4 == 0 && offset >= 0 && offset % 4 == 0,
+                 "allgather_f32: n_per_rank and offset must be multiples of 4 elements");
+  ctas = ctas_for(n_per_rank / kBlock, ctas);
+  allgather_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, n_per_rank / 4);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_p2p_copy(const b200_comm* comm, int32_t peer, int64_t offset, int64_t n, int32_t pull, void* stream) {
+  CommDev d;
+  int ctas;
+  if (int e = to_dev(comm, d, ctas)) return e;
+  B200_CHECK_ARG(peer >= 0 && peer < d.world && peer != d.rank && n > 0 && n % 4 == 0 && offset >= 0 && offset % 4 == 0,
+                 "p2p_copy: peer must be another rank; n and offset multiples of 4 elements");
+  ctas = ctas_for(n / kBlock, ctas);
+  p2p_copy_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, peer, offset, n / 4, pull);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_p2p_pingpong(const b200_comm* comm, int32_t rank_a, int32_t rank_b, int64_t offset, int64_t n, int32_t iters,
+                      float* out_us, void* stream) {
+  CommDev d;
+  int ctas;
+  if (int e = to_dev(comm, d, ctas)) return e;
+  B200_CHECK_ARG(rank_a >= 0 && rank_a < d.world && rank_b >= 0 && rank_b < d.world && rank_a != rank_b && iters > 0 &&
+                     n >= 0 && n % 4 == 0 && n <= (1 << 22) && offset >= 0 && offset % 4 == 0,
+                 "p2p_pingpong: two distinct ranks, n a multiple of 4 elements (<= 4 Mi), iters > 0");
+  p2p_pingpong_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, rank_a, rank_b, offset, (int)(n / 4), iters,
+                                                                           out_us);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -14,7 +14,8 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ w, fl
                                                        int64_t nblk, const int32_t* __restrict__ block_tensor,
                                                        const float* __restrict__ tdecay, const float* __restrict__ tlars,
                                                        const float* __restrict__ trust, float lr, float mu, float wd,
-                                                       float gscale) {
+                                                       float gscale, const float* __restrict__ lr_dev) {
+  if (lr_dev) lr = __ldg(lr_dev);    // a schedule can change the rate under a captured CUDA graph
   // one CTA handles one 1024-element block per iteration: 256 threads x float4
   for (int64_t b = blockIdx.x; b < nblk; b += gridDim.x) {
     float dec = wd, tr = 1.0f;
@@ -167,7 +168,8 @@ extern "C" {
 
 int b200_sgd_momentum_flat(float* master, float* mom, const float* grad, b200_bf16* shadow, int64_t n,
                            const int32_t* block_tensor, const float* tensor_decay, const float* tensor_lars,
-                           const float* trust, float lr, float mu, float wd, float grad_scale, void* stream) {
+                           const float* trust, float lr, float mu, float wd, float grad_scale, const float* lr_dev,
+                           void* stream) {
   B200_CHECK_ARG(master && mom && grad, "sgd_momentum_flat: null pointer");
   B200_CHECK_ARG(n > 0 && n % 1024 == 0, "sgd_momentum_flat: n must be a positive multiple of 1024");
   B200_CHECK_ARG(!block_tensor || tensor_decay, "sgd_momentum_flat: block table needs tensor_decay");
@@ -176,7 +178,7 @@ int b200_sgd_momentum_flat(float* master, float* mom, const float* grad, b200_bf
   int grid = (int)(nblk < (int64_t)kNumSMs * 8 ? nblk : (int64_t)kNumSMs * 8);
   sgd_flat_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(master, mom, grad, shadow, nblk, block_tensor,
                                                                       tensor_decay, tensor_lars, trust, lr, mu, wd,
-                                                                      grad_scale);
+                                                                      grad_scale, lr_dev);
   B200_LAUNCH_CHECK();
   return 0;
 }

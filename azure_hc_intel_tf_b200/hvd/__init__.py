@@ -194,21 +194,33 @@ def allgather(tensor: torch.Tensor, name: Optional[str] = None) -> torch.Tensor:
     n = size()
     if n == 1:
         return tensor.clone()
-    sizes = [torch.zeros(1, dtype=torch.int64, device=tensor.device) for _ in range(n)]
-    dist.all_gather(sizes, torch.tensor([tensor.shape[0]], dtype=torch.int64, device=tensor.device))
+    ctx = _state.get("symm") if tensor.is_cuda else None
+    mine = torch.tensor([tensor.shape[0]], dtype=torch.int64, device=tensor.device)
+    if ctx is not None:
+        sizes = ctx.allgather_tensor(mine)              # own all-gather kernel over NVLink
+    else:
+        sizes = [torch.zeros(1, dtype=torch.int64, device=tensor.device) for _ in range(n)]
+        dist.all_gather(sizes, mine)
     sizes = [int(s.item()) for s in sizes]
     mx = max(sizes)
     pad = tensor.new_zeros((mx,) + tuple(tensor.shape[1:]))
     pad[: tensor.shape[0]] = tensor
-    outs = [torch.empty_like(pad) for _ in range(n)]
-    dist.all_gather(outs, pad)
+    if ctx is not None:
+        outs = ctx.allgather_tensor(pad)
+    else:
+        outs = [torch.empty_like(pad) for _ in range(n)]
+        dist.all_gather(outs, pad)
     return torch.cat([o[:s] for o, s in zip(outs, sizes)], dim=0)
 
 
 def broadcast_(tensor: torch.Tensor, root_rank: int = 0, name: Optional[str] = None) -> torch.Tensor:
     _need()
     if size() > 1:
-        dist.broadcast(tensor, src=root_rank)
+        ctx = _state.get("symm")
+        if ctx is not None and tensor.is_cuda:
+            ctx.broadcast_tensor_(tensor, root_rank)     # own NVLink broadcast kernel (K-BC)
+        else:
+            dist.broadcast(tensor, src=root_rank)
     return tensor
 
 
@@ -229,7 +241,11 @@ def poll(handle: _Handle) -> bool:
 def barrier() -> None:
     _need()
     if size() > 1:
-        dist.barrier()
+        ctx = _state.get("symm")
+        if ctx is not None:
+            ctx.host_barrier()                           # flag barrier kernel over NVLink + stream wait
+        else:
+            dist.barrier()
 
 
 def broadcast_parameters(params, root_rank: int = 0) -> None:
@@ -250,7 +266,7 @@ def broadcast_parameters(params, root_rank: int = 0) -> None:
     ctx = _state.get("symm")
     for (_dt, _dev), ts in by_key.items():
         flat = torch.cat([t.detach().reshape(-1) for t in ts])
-        if ctx is not None and flat.is_cuda and flat.dtype == torch.float32:
+        if ctx is not None and flat.is_cuda:
             ctx.broadcast_tensor_(flat, root_rank)       # own NVLink broadcast kernel (K-BC), no NCCL
         else:
             dist.broadcast(flat, src=root_rank)
@@ -279,9 +295,7 @@ def broadcast_optimizer_state(optimizer, root_rank: int = 0) -> None:
             if isinstance(v, torch.Tensor):
                 tensors[f"{pid}.{k}"] = v
     broadcast_parameters(tensors, root_rank)
-    objs = [state.get("param_groups")]
-    dist.broadcast_object_list(objs, src=root_rank)
-    state["param_groups"] = objs[0]
+    state["param_groups"] = broadcast_object(state.get("param_groups"), root_rank)
     opt.load_state_dict(state)
 
 
@@ -289,6 +303,17 @@ def broadcast_object(obj, root_rank: int = 0):
     _need()
     if size() == 1:
         return obj
+    ctx = _state.get("symm")
+    if ctx is not None:
+        import pickle
+        dev = _state["device"]
+        raw = pickle.dumps(obj) if rank() == root_rank else b""
+        n = broadcast_(torch.tensor([len(raw)], dtype=torch.int64, device=dev), root_rank)
+        buf = torch.empty(int(n.item()), dtype=torch.uint8, device=dev)
+        if rank() == root_rank:
+            buf.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        broadcast_(buf, root_rank)
+        return pickle.loads(bytes(buf.cpu().numpy()))
     objs = [obj]
     dist.broadcast_object_list(objs, src=root_rank)
     return objs[0]

@@ -11,7 +11,7 @@ What happens here instead:
   of the weights are *views into flat buffers laid out in plan order*, so there is no copy-in/copy-out;
 * when the last gradient of a bucket lands, one kernel launch handles the whole bucket. On fabric
   ``nvl`` that kernel reduces the peers' buffers over NVLink, applies 1/N, weight decay and the
-  momentum/LARS update, and writes fp32 master + bf16 working weights (csrc/comm/fused_allreduce_sgd.cu).
+  momentum/LARS update, and writes fp32 master + bf16 working weights (csrc/comm/allreduce.cu).
   On ``nccl``/``gloo`` the allreduce is the library's and the update is a separate flat kernel;
 * ``step()`` only waits for the side stream.
 """
@@ -107,12 +107,55 @@ class MomentumSGD:
         self.tensor_lars = torch.tensor([1.0 if f & FLAG_LARS else 0.0 for f in flags], dtype=torch.float32, device=dev)
         self.trust = torch.ones(len(flags), dtype=torch.float32, device=dev)
         self.norms = torch.zeros(2 * len(flags), dtype=torch.float32, device=dev)
+        # the learning rate also lives in device memory: the update kernels read it from there, so a schedule (warm-up,
+        # decay) keeps working when the whole step is replayed from a CUDA graph
+        self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        self.lr_schedule = None
+        self._lars_tab = None
         self.steps = 0
 
     # -- torch.optim-like surface
     @property
     def lr(self):
         return self.param_groups[0]["lr"]
+
+    def set_lr(self, lr: float):
+        """Change the learning rate (host copy and the device scalar the kernels read)."""
+        lr = float(lr)
+        if lr != self.param_groups[0]["lr"]:
+            self.param_groups[0]["lr"] = lr
+            if self.lr_dev is not None:
+                self.lr_dev.fill_(lr)
+
+    def apply_schedule(self):
+        """Set the rate for the step about to run from ``lr_schedule(step)`` (utils/lr_schedule.py), if one is set."""
+        if self.lr_schedule is None:
+            return
+        if self.master.is_cuda and torch.cuda.is_current_stream_capturing():
+            return      # a fill captured into the graph would reset the rate on every replay; the caller sets it outside
+        self.set_lr(self.lr_schedule(self.steps))
+
+    def lars_tables(self, block: int):
+        """(per-block partial-norm buffer, first block of each tensor, blocks of each tensor), in units of ``block``
+        elements, for the fused allreduce+LARS kernel (include/b200comm.h)."""
+        if self._lars_tab is None or self._lars_tab[0] != block:
+            lo = torch.tensor([s // block for s, _ in self.ranges], dtype=torch.int32, device=self.device)
+            cnt = torch.tensor([(n + block - 1) // block for _, n in self.ranges], dtype=torch.int32, device=self.device)
+            part = torch.zeros(2 * (self.total // block), dtype=torch.float32, device=self.device)
+            self._lars_tab = (block, part, lo, cnt)
+        return self._lars_tab[1:]
+
+    def lars_bucket_args(self, b: int, block: int):
+        """(t_lo, t_hi, upd_lo, upd_hi) for bucket b: the tensors whose last element lies in the bucket, and the block
+        range they span (which starts in an earlier bucket when the first of them was split by the planner)."""
+        lo, hi = self.bucket_range(b)
+        ends = [i for i, (s, n) in enumerate(self.ranges) if lo < s + n <= hi]
+        if not ends:
+            return 0, 0, 0, 0
+        t_lo, t_hi = ends[0], ends[-1] + 1
+        s0 = self.ranges[t_lo][0]
+        s1, n1 = self.ranges[t_hi - 1]
+        return t_lo, t_hi, s0 // block, (s1 + n1 + block - 1) // block
 
     def zero_grad(self, set_to_none: bool = False):
         self.grad.zero_()
@@ -171,6 +214,7 @@ class MomentumSGD:
 
     def step(self, closure=None):
         loss = closure() if closure is not None else None
+        self.apply_schedule()
         self.compute_trust()
         self.update_range(0, self.total)
         self.steps += 1
@@ -192,14 +236,21 @@ class MomentumSGD:
                 self.shadow.copy_(self.master)
         self.steps = sd.get("steps", 0)
         self.param_groups[0].update(sd["param_groups"][0])
+        if self.lr_dev is not None:
+            self.lr_dev.fill_(float(self.param_groups[0]["lr"]))
 
     def momentum_of(self, p) -> torch.Tensor:
         s, n = self.ranges[p.flat_index]
         return _physical_view(self.mom[s:s + n], p)
 
     def broadcast_state(self, root_rank: int = 0):
-        dist.broadcast(self.master, src=root_rank)
-        dist.broadcast(self.mom, src=root_rank)
+        from . import symmetric_context
+        ctx = symmetric_context()
+        for t in (self.master, self.mom):
+            if ctx is not None and t.is_cuda:
+                ctx.broadcast_tensor_(t, root_rank)      # own NVLink broadcast kernel, no NCCL
+            else:
+                dist.broadcast(t, src=root_rank)
         if self.shadow is not None:
             self.shadow.copy_(self.master)
 
@@ -278,7 +329,15 @@ class DistributedOptimizer:
             lib = _native.host()
             self._stall = (lib, lib.hvd_stall_start(self.tracker._h, min(5.0, warn_s / 2), warn_s, abort_s))
         self._cuda = self.grad.is_cuda
-        self._comm_stream = torch.cuda.Stream(priority=-1) if self._cuda else None
+        # on the NVLink fabric every collective of this process runs on the context's one communication stream (the
+        # kernels share per-CTA flag slots and must never overlap each other); otherwise a private side stream
+        if self._cuda and self._symm is not None:
+            self._comm_stream = self._symm.stream
+        else:
+            self._comm_stream = torch.cuda.Stream(priority=-1) if self._cuda else None
+        self._tl_events, self._tl_base = [], None
+        self._ready = set()          # buckets whose gradients are complete but that wait for an earlier bucket
+        self._next = 0               # buckets are launched in plan order: the same order on every rank by construction
         self._handles = []
         self._comm_used = False      # the side stream holds work the compute stream has not joined yet
         self._launched = set()
@@ -288,7 +347,9 @@ class DistributedOptimizer:
         self._hooks = []
         for i, p in enumerate(self.params):
             self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
-            p.grad_ready = self._make_direct(i)
+            # The kernels' direct hand-off OVERWRITES the gradient view. With several backward passes per step the
+            # passes must add up, so the hand-off is left off and autograd accumulates into the view itself.
+            p.grad_ready = self._make_direct(i) if self.passes == 1 else None
         self.tracker.begin_step()
 
     # -- plumbing
@@ -313,7 +374,11 @@ class DistributedOptimizer:
         if self._counts[i] < self.passes:
             return
         for b in self.tracker.ready(i):
-            self._launch(b)
+            self._ready.add(b)
+        while self._next in self._ready:
+            self._ready.discard(self._next)
+            self._launch(self._next)
+            self._next += 1
 
     def _check_plan(self):
         if self._plan_checked or self.world == 1:
@@ -321,9 +386,13 @@ class DistributedOptimizer:
             return
         h = torch.tensor([self.plan.hash & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64,
                          device=self.grad.device if self.fabric != "gloo" else "cpu")
-        lo, hi = h.clone(), h.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        if self._symm is not None and h.is_cuda:
+            every = torch.cat(self._symm.allgather_tensor(h))        # own all-gather kernel
+            lo, hi = every.min(), every.max()
+        else:
+            lo, hi = h.clone(), h.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         if int(lo.item()) != int(hi.item()):
             raise RuntimeError("fusion plans differ between ranks (models or thresholds are not identical)")
         self._plan_checked = True
@@ -337,6 +406,19 @@ class DistributedOptimizer:
         lo, hi = self._range(b)
         scale = 1.0 / (self.world * self.passes) if self.op == "average" else 1.0 / self.passes
         t0 = self.timeline.now_us() if self.timeline is not None else 0.0
+        # device-timed timeline (HOROVOD_TIMELINE): per bucket an event when its last gradient is ready (compute
+        # stream), when its collective starts and when it is done (communication stream). Not under graph capture.
+        tl_dev = (self.timeline is not None and self._cuda and self.world > 1
+                  and not torch.cuda.is_current_stream_capturing())
+        ev = None
+        if tl_dev:
+            if not self._tl_events:
+                self._tl_base = (torch.cuda.Event(enable_timing=True), self.timeline.now_us())
+                self._tl_base[0].record()
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev[0].record()
+        if self.fused and b == 0:
+            self._opt.apply_schedule()       # before the first update of the step (the rate is a device scalar)
         if self.world == 1:
             if self.fused and not self._opt.lars:
                 self._opt.update_range(lo, hi, scale)
@@ -345,12 +427,13 @@ class DistributedOptimizer:
         if self._cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream())
             self._comm_used = True
+        if ev is not None:
+            ev[1].record(self._comm_stream)
         if self.fused and self._symm is not None:
             with torch.cuda.stream(self._comm_stream):
-                if self._opt.lars:
-                    self._symm.allreduce_range_(self._symm_grad, lo, hi, 1.0)
-                else:
-                    self._symm.fused_allreduce_sgd(self._symm_grad, self._opt, lo, hi, scale)
+                # one launch per bucket either way; LARS folds the norms of the tensors that end in this bucket
+                lars = self._opt.lars_bucket_args(b, self._symm.block) if self._opt.lars else None
+                self._symm.fused_allreduce_sgd(self._symm_grad, self._opt, lo, hi, scale, lars=lars)
             self._handles.append((b, None, scale))
         else:
             chunk = self.grad[lo:hi]
@@ -363,13 +446,17 @@ class DistributedOptimizer:
             self._handles.append((b, (work, wire, cctx, chunk), scale))
         if self.timeline is not None:
             self.timeline.event(f"bucket{b}", "LAUNCH", 1, t0, self.timeline.now_us() - t0)
+        if ev is not None:
+            ev[2].record(self._comm_stream)
+            self._tl_events.append((b, hi - lo, ev))
 
     def synchronize(self):
         """Launch whatever has not been launched (unused parameters), then wait for all buckets."""
         self._check_plan()
-        for b in range(len(self.plan.buckets)):
-            if b not in self._launched:
-                self._launch(b)
+        while self._next < len(self.plan.buckets):        # unused parameters: their buckets never became ready
+            self._launch(self._next)
+            self._next += 1
+        self._ready.clear()
         pending_update = []
         for b, h, scale in self._handles:
             if h is not None:
@@ -387,7 +474,8 @@ class DistributedOptimizer:
             on_side = self._cuda and self._comm_used
             stream_ctx = torch.cuda.stream(self._comm_stream) if on_side else _null()
             with stream_ctx:
-                if self._opt.lars:
+                if self._opt.lars and not (self._symm is not None and self.world > 1):
+                    # library fabrics and single process: norms and update after the (library) allreduce
                     scale = 1.0 / (self.world * self.passes) if self.op == "average" else 1.0 / self.passes
                     self._opt.compute_trust(scale)
                     self._opt.update_range(0, self._opt.total, scale)
@@ -413,15 +501,34 @@ class DistributedOptimizer:
     def step(self, closure=None):
         loss = closure() if closure is not None else None
         self.synchronize()
+        self._flush_timeline()
         if self.fused:
             self._opt.steps += 1
         else:
             self._opt.step()
         self._launched.clear()
+        self._next = 0
         self._counts = [0] * len(self.params)
         self._direct_seen = [False] * len(self.params)
         self.tracker.begin_step()
         return loss
+
+    def _flush_timeline(self):
+        """Write the device-side times of this step's buckets: QUEUE = last gradient ready → collective starts,
+        ALLREDUCE_UPDATE = the fused kernel (or the library allreduce) on the communication stream. Times come from
+        CUDA events, placed on the host clock through one base event per step."""
+        if not self._tl_events:
+            return
+        torch.cuda.synchronize()
+        base_ev, base_us = self._tl_base
+        for b, numel, (ready, start, done) in self._tl_events:
+            t_ready = base_us + base_ev.elapsed_time(ready) * 1e3
+            t_start = base_us + base_ev.elapsed_time(start) * 1e3
+            t_done = base_us + base_ev.elapsed_time(done) * 1e3
+            name = f"bucket{b} ({numel * 4 >> 10} KiB)"
+            self.timeline.event(name, "QUEUE", 2, t_ready, max(0.0, t_start - t_ready))
+            self.timeline.event(name, "ALLREDUCE_UPDATE", 3, t_start, max(0.0, t_done - t_start))
+        self._tl_events, self._tl_base = [], None
 
     def close(self):
         """Stop the stall inspector thread (also called on garbage collection)."""

@@ -14,7 +14,7 @@ def sgd_update(opt, lo: int, hi: int, lr: float, mu: float, wd: float, grad_scal
     _check(lib().b200_sgd_momentum_flat(_ptr(opt.master[lo:]), _ptr(opt.mom[lo:]), _ptr(opt.grad[lo:]), _ptr(shadow),
                                         hi - lo, _ptr(blk), _ptr(opt.tensor_decay), _ptr(opt.tensor_lars),
                                         _ptr(opt.trust) if opt.lars else _ptr(None), lr, mu, wd, grad_scale,
-                                        _stream()), "sgd_momentum_flat")
+                                        _ptr(getattr(opt, "lr_dev", None)), _stream()), "sgd_momentum_flat")
 
 
 def lars_trust(opt, wd: float, grad_scale: float):

@@ -176,8 +176,12 @@ def launch(num_nodes: int, workers_per_socket: int, batch_size: int, fabric: str
         env = dict(os.environ)
         env.update(RANK=str(node_rank * wpn + lr), LOCAL_RANK=str(lr), WORLD_SIZE=str(total),
                    LOCAL_WORLD_SIZE=str(wpn), MASTER_ADDR=master_addr, MASTER_PORT=str(master_port),
-                   OMP_NUM_THREADS=str(max(1, layout.intra_threads)),
-                   HOROVOD_FUSION_THRESHOLD=os.environ.get("HOROVOD_FUSION_THRESHOLD", str(FUSION_THRESHOLD)))
+                   OMP_NUM_THREADS=str(max(1, layout.intra_threads)))
+        # The reference exports HOROVOD_FUSION_THRESHOLD=134217728 to every rank (:105). A value the user set is
+        # forwarded as is; otherwise the library fabrics get the reference's 128 MiB and the NVLink fabric keeps its
+        # own default (16 MiB buckets that overlap with backward; utils/flags.py resolve_fusion_threshold).
+        if "HOROVOD_FUSION_THRESHOLD" not in os.environ and fabric not in ("nvl", "ib"):
+            env["HOROVOD_FUSION_THRESHOLD"] = str(FUSION_THRESHOLD)
         sock = min(lr // per_socket, cpu["sockets"] - 1) if workers_per_socket else 0
         if topo is not None and lr < len(topo.gpus) and 0 <= topo.numa_of(lr) < cpu["sockets"]:
             sock = topo.numa_of(lr)      # pin the worker next to the NUMA node its GPU hangs off

@@ -11,6 +11,7 @@ rendezvous only — never for a gradient.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import os
 from typing import List, Optional
@@ -26,13 +27,20 @@ MAX_RANKS = 8
 class CommStruct(C.Structure):
     _fields_ = [("buf", C.c_uint64 * MAX_RANKS), ("pad", C.c_uint64 * MAX_RANKS), ("rank", C.c_int32),
                 ("world", C.c_int32), ("ctas", C.c_int32), ("one_shot_max_bytes", C.c_int32),
-                ("mc", C.c_uint64), ("nvls_min_bytes", C.c_int64)]
+                ("mc", C.c_uint64), ("nvls_min_bytes", C.c_int64), ("algo", C.c_int32), ("reserved", C.c_int32)]
+
+
+ALGO_AUTO, ALGO_ONE_SHOT, ALGO_TWO_SHOT, ALGO_NVLS = 0, 1, 2, 3
+ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONE_SHOT, "twoshot": ALGO_TWO_SHOT, "nvls": ALGO_NVLS}
 
 
 class SgdArgs(C.Structure):
     _fields_ = [("master", C.c_void_p), ("mom", C.c_void_p), ("shadow", C.c_void_p), ("block_tensor", C.c_void_p),
                 ("tensor_decay", C.c_void_p), ("tensor_lars", C.c_void_p), ("trust", C.c_void_p),
-                ("lr", C.c_float), ("mu", C.c_float), ("wd", C.c_float)]
+                ("lr", C.c_float), ("mu", C.c_float), ("wd", C.c_float), ("lr_dev", C.c_void_p),
+                ("lars_block_partials", C.c_void_p), ("tensor_blk_lo", C.c_void_p), ("tensor_blk_cnt", C.c_void_p),
+                ("lars_t_lo", C.c_int32), ("lars_t_hi", C.c_int32), ("lars_upd_lo", C.c_int64),
+                ("lars_upd_hi", C.c_int64), ("lars_eta", C.c_float), ("lars_eps", C.c_float)]
 
 
 class _DevArray:
@@ -58,6 +66,11 @@ def _declare(lib):
     lib.b200_symm_open_handle.argtypes, lib.b200_symm_open_handle.restype = [vp, C.POINTER(vp)], i32
     lib.b200_symm_close_handle.argtypes, lib.b200_symm_close_handle.restype = [vp], i32
     lib.b200_comm_pad_bytes.argtypes, lib.b200_comm_pad_bytes.restype = [], i64
+    lib.b200_comm_block_elems.argtypes, lib.b200_comm_block_elems.restype = [], i32
+    lib.b200_allgather_f32.argtypes, lib.b200_allgather_f32.restype = [C.POINTER(CommStruct), i64, i64, vp], i32
+    lib.b200_p2p_copy.argtypes, lib.b200_p2p_copy.restype = [C.POINTER(CommStruct), i32, i64, i64, i32, vp], i32
+    lib.b200_p2p_pingpong.argtypes = [C.POINTER(CommStruct), i32, i32, i64, i64, i32, vp, vp]
+    lib.b200_p2p_pingpong.restype = i32
     lib.b200_allreduce_f32.argtypes = [C.POINTER(CommStruct), i64, i64, C.c_float, C.POINTER(SgdArgs), vp]
     lib.b200_allreduce_f32.restype = i32
     lib.b200_allreduce_bf16.argtypes = [C.POINTER(CommStruct), i64, i64, C.c_float, vp]
@@ -129,19 +142,31 @@ class McSymmBuffer:
 
 
 class SymmetricContext:
+    """Per-process handle on the NVLink fabric: the signal pad, the symmetric buffers and the collectives.
+
+    Every kernel that uses the signal pad shares its per-CTA epoch slots, so two of them must never be in flight on
+    one device at the same time. All collectives are therefore issued on ONE stream, ``self.stream`` (high priority);
+    a call made from any other stream forks onto it and joins back (``_serial``), and ``DistributedOptimizer`` uses
+    this same stream as its side stream. The fork/join pattern is also what a CUDA-graph capture needs."""
+
     def __init__(self, rank: int, world: int, device: torch.device):
         if world > MAX_RANKS:
             raise ValueError(f"the NVLink fabric supports up to {MAX_RANKS} ranks on one box, got {world}")
         self.rank, self.world, self.device = rank, world, device
         self.lib = _native.cuda()
         _declare(self.lib)
-        self.ctas = int(os.environ.get("B200_COMM_CTAS", "48"))
+        self.block = int(self.lib.b200_comm_block_elems())
+        # upper bound on CTAs per collective (128 threads each); small messages use fewer (one per four blocks)
+        self.ctas = int(os.environ.get("B200_COMM_CTAS", "96"))
         # messages up to this many bytes use the one-shot kernel (one NVLink traversal); 0 disables it
         self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(128 << 10)))
         # messages of at least this many bytes use the NVLS (in-switch reduction) kernel when the buffer has a
-        # multicast mapping; -1 disables NVLS
-        self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(8 << 20)))
+        # multicast mapping; -1 disables NVLS. With two ranks a direct peer read is the shorter path.
+        default_nvls = (8 << 20) if world > 2 else -1
+        self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(default_nvls)))
+        self.algo = ALGOS[os.environ.get("B200_COMM_ALGO", "auto")]
         self.nvls_ok = None      # decided collectively at the first multicast allocation
+        self.stream = torch.cuda.Stream(device=device, priority=-1)
         self.buffers: List[SymmBuffer] = []
         self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
         self._scratch: Optional[SymmBuffer] = None
@@ -163,12 +188,12 @@ class SymmetricContext:
     def alloc(self, nbytes: int, dtype: torch.dtype, multicast: bool = False):
         """Collective. ``multicast=True`` asks for a buffer with an NVLS multicast mapping and falls back to a plain
         IPC buffer (on every rank alike) if the platform refuses."""
-        if multicast and self.nvls_min_bytes >= 0 and self.nvls_ok is not False:
+        if multicast and self.nvls_ok is not False and os.environ.get("B200_COMM_MULTICAST", "1") != "0":
             b, ok = None, 1
             try:
                 b = McSymmBuffer(self, nbytes, dtype)
                 ok = 1 if b.mc_ptr else 0
-            except Exception as e:          # no VMM/multicast support, or the private API changed
+            except Exception as e:          # no VMM/multicast support on this platform
                 ok = 0
                 if self.rank == 0:
                     print(f"[b200 comm] NVLS multicast unavailable ({e.__class__.__name__}: {e}); using P2P two-shot")
@@ -179,6 +204,8 @@ class SymmetricContext:
                 self.buffers.append(b)
                 dist.barrier()
                 return b
+            if b is not None:
+                b.close()
         b = SymmBuffer(self, nbytes, dtype)
         self.buffers.append(b)
         dist.barrier()           # every rank has mapped every peer before anyone launches a kernel on it
@@ -187,7 +214,7 @@ class SymmetricContext:
     def alloc_like_flat(self, numel: int, dtype: torch.dtype, multicast: bool = False):
         return self.alloc(numel * torch.empty((), dtype=dtype).element_size(), dtype, multicast)
 
-    def comm_struct(self, buf: SymmBuffer) -> CommStruct:
+    def comm_struct(self, buf: SymmBuffer, algo: Optional[int] = None) -> CommStruct:
         cs = CommStruct()
         for r in range(self.world):
             cs.buf[r] = buf.peers[r]
@@ -195,45 +222,106 @@ class SymmetricContext:
         cs.rank, cs.world, cs.ctas, cs.one_shot_max_bytes = self.rank, self.world, self.ctas, self.one_shot_max_bytes
         cs.mc = getattr(buf, "mc_ptr", 0) or 0
         cs.nvls_min_bytes = self.nvls_min_bytes
+        cs.algo = self.algo if algo is None else algo
         return cs
 
     @staticmethod
     def _stream():
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
+    @contextlib.contextmanager
+    def _serial(self):
+        """Run the body on the communication stream, ordered after the caller's stream, and make the caller's
+        stream wait for it (no-op when the caller already is on the communication stream)."""
+        cur = torch.cuda.current_stream()
+        if cur.cuda_stream == self.stream.cuda_stream:
+            yield
+            return
+        self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            yield
+        cur.wait_stream(self.stream)
+
     # -- collectives on symmetric buffers
-    def allreduce_range_(self, buf: SymmBuffer, lo: int, hi: int, scale: float = 1.0):
-        """In-place sum (times scale) of fp32 elements [lo, hi) of ``buf`` across ranks."""
-        cs = self.comm_struct(buf)
-        if buf.local.dtype == torch.float32:
-            _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, None, self._stream()), "allreduce_f32")
-        elif buf.local.dtype == torch.bfloat16:
-            _check(self.lib.b200_allreduce_bf16(C.byref(cs), lo, hi - lo, scale, self._stream()), "allreduce_bf16")
-        else:
-            raise TypeError(buf.local.dtype)
+    def allreduce_range_(self, buf: SymmBuffer, lo: int, hi: int, scale: float = 1.0, algo: Optional[int] = None):
+        """In-place sum (times scale) of elements [lo, hi) of ``buf`` across ranks."""
+        cs = self.comm_struct(buf, algo)
+        with self._serial():
+            if buf.local.dtype == torch.float32:
+                _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, None, self._stream()), "allreduce_f32")
+            elif buf.local.dtype == torch.bfloat16:
+                _check(self.lib.b200_allreduce_bf16(C.byref(cs), lo, hi - lo, scale, self._stream()), "allreduce_bf16")
+            else:
+                raise TypeError(buf.local.dtype)
         self._count()
 
-    def fused_allreduce_sgd(self, buf: SymmBuffer, opt, lo: int, hi: int, scale: float):
+    def fused_allreduce_sgd(self, buf: SymmBuffer, opt, lo: int, hi: int, scale: float, lars=None):
         """One launch: allreduce [lo, hi) of the symmetric gradient buffer, 1/N scale, momentum-SGD update of
-        ``opt``'s local master / momentum / bf16 weights."""
+        ``opt``'s local master / momentum / bf16 weights. ``lars`` = (t_lo, t_hi, upd_lo_blk, upd_hi_blk) switches
+        on the fused LARS half for the tensors that end in this bucket (see include/b200comm.h)."""
         g = opt.param_groups[0]
-        a = SgdArgs(opt.master.data_ptr(), opt.mom.data_ptr(), opt.shadow.data_ptr() if opt.shadow is not None else None,
-                    opt.block_tensor.data_ptr(), opt.tensor_decay.data_ptr(), opt.tensor_lars.data_ptr(),
-                    opt.trust.data_ptr() if opt.lars else None, g["lr"], g["momentum"], g["weight_decay"])
+        a = SgdArgs()
+        a.master, a.mom = opt.master.data_ptr(), opt.mom.data_ptr()
+        a.shadow = opt.shadow.data_ptr() if opt.shadow is not None else None
+        a.block_tensor, a.tensor_decay = opt.block_tensor.data_ptr(), opt.tensor_decay.data_ptr()
+        a.tensor_lars = opt.tensor_lars.data_ptr()
+        a.trust = opt.trust.data_ptr() if opt.lars else None
+        a.lr, a.mu, a.wd = g["lr"], g["momentum"], g["weight_decay"]
+        a.lr_dev = opt.lr_dev.data_ptr() if getattr(opt, "lr_dev", None) is not None else None
+        if lars is not None:
+            part, blk_lo, blk_cnt = opt.lars_tables(self.block)
+            a.lars_block_partials, a.tensor_blk_lo, a.tensor_blk_cnt = part.data_ptr(), blk_lo.data_ptr(), blk_cnt.data_ptr()
+            a.lars_t_lo, a.lars_t_hi, a.lars_upd_lo, a.lars_upd_hi = lars
+            a.lars_eta, a.lars_eps = opt.lars_eta, opt.lars_eps
         cs = self.comm_struct(buf)
-        _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, C.byref(a), self._stream()),
-               "fused allreduce+sgd")
+        with self._serial():
+            _check(self.lib.b200_allreduce_f32(C.byref(cs), lo, hi - lo, scale, C.byref(a), self._stream()),
+                   "fused allreduce+sgd")
         self._count()
 
     def barrier(self):
+        """Device-side barrier across ranks on the communication stream (no host synchronisation)."""
         cs = self.comm_struct(self.pad)
-        _check(self.lib.b200_comm_barrier(C.byref(cs), self._stream()), "comm_barrier")
+        with self._serial():
+            _check(self.lib.b200_comm_barrier(C.byref(cs), self._stream()), "comm_barrier")
         self._count()
+
+    def host_barrier(self):
+        """hvd.barrier(): every rank has reached this point when it returns (flag kernel + stream wait)."""
+        self.barrier()
+        torch.cuda.current_stream().synchronize()
 
     def broadcast_(self, buf: SymmBuffer, lo: int, hi: int, root: int):
         cs = self.comm_struct(buf)
-        _check(self.lib.b200_broadcast_f32(C.byref(cs), lo, hi - lo, root, self._stream()), "broadcast_f32")
+        with self._serial():
+            _check(self.lib.b200_broadcast_f32(C.byref(cs), lo, hi - lo, root, self._stream()), "broadcast_f32")
         self._count()
+
+    def allgather_(self, buf: SymmBuffer, lo: int, n_per_rank: int):
+        """Rank r's fp32 segment [lo + r*n, +n) of ``buf`` is replicated into every rank's ``buf``."""
+        cs = self.comm_struct(buf)
+        with self._serial():
+            _check(self.lib.b200_allgather_f32(C.byref(cs), lo, n_per_rank, self._stream()), "allgather_f32")
+        self._count()
+
+    def p2p_copy(self, buf: SymmBuffer, peer: int, lo: int, n: int, pull: bool = False):
+        """Bandwidth probe: move n floats to (or, ``pull``, from) one peer. Not serialised: it uses no flags."""
+        cs = self.comm_struct(buf)
+        _check(self.lib.b200_p2p_copy(C.byref(cs), peer, lo, n, int(pull), self._stream()), "p2p_copy")
+        self._count()
+
+    def p2p_pingpong(self, buf: SymmBuffer, a: int, b: int, n: int, iters: int, out_us: torch.Tensor):
+        cs = self.comm_struct(buf)
+        with self._serial():
+            _check(self.lib.b200_p2p_pingpong(C.byref(cs), a, b, 0, n, iters, C.c_void_p(out_us.data_ptr()),
+                                              self._stream()), "p2p_pingpong")
+        self._count()
+
+    def _staging(self, need_bytes: int) -> SymmBuffer:
+        if self._scratch is None or self._scratch.nbytes < need_bytes:
+            # sized collectively: every rank reaches this branch for the same call
+            self._scratch = self.alloc(max(need_bytes, 64 << 20), torch.uint8, multicast=True)
+        return self._scratch
 
     def allreduce_(self, tensor: torch.Tensor, scale: float = 1.0):
         """Allreduce an arbitrary CUDA tensor (fp32 / bf16) by staging it through a symmetric scratch buffer.
@@ -242,37 +330,49 @@ class SymmetricContext:
         esz = flat.element_size()
         gran = 1024 if flat.dtype == torch.float32 else 2048
         n = (flat.numel() + gran - 1) // gran * gran
-        need = n * 4
-        if self._scratch is None or self._scratch.nbytes < need:
-            # sized collectively: every rank reaches this branch for the same call
-            self._scratch = self.alloc(max(need, 64 << 20), torch.uint8)
-        view = self._scratch.local_bytes[: n * esz].view(flat.dtype)
+        sc = self._staging(n * 4)
+        view = sc.local_bytes[: n * esz].view(flat.dtype)
         view[: flat.numel()].copy_(flat)
         if n > flat.numel():
             view[flat.numel():].zero_()
-        cs = self.comm_struct(self._scratch)
-        if flat.dtype == torch.float32:
-            _check(self.lib.b200_allreduce_f32(C.byref(cs), 0, n, scale, None, self._stream()), "allreduce_f32")
-        else:
-            _check(self.lib.b200_allreduce_bf16(C.byref(cs), 0, n, scale, self._stream()), "allreduce_bf16")
+        cs = self.comm_struct(sc)
+        with self._serial():
+            if flat.dtype == torch.float32:
+                _check(self.lib.b200_allreduce_f32(C.byref(cs), 0, n, scale, None, self._stream()), "allreduce_f32")
+            else:
+                _check(self.lib.b200_allreduce_bf16(C.byref(cs), 0, n, scale, self._stream()), "allreduce_bf16")
         self._count()
         flat.copy_(view[: flat.numel()])
         return tensor
 
     def broadcast_tensor_(self, tensor: torch.Tensor, root: int):
-        """Broadcast an ordinary fp32 CUDA tensor from ``root`` by staging it through symmetric scratch: the root
-        writes every peer's copy with the broadcast kernel (Horovod's broadcast_global_variables role)."""
-        flat = tensor.reshape(-1)
-        n = (flat.numel() + 3) // 4 * 4
-        need = n * 4
-        if self._scratch is None or self._scratch.nbytes < need:
-            self._scratch = self.alloc(max(need, 64 << 20), torch.uint8)
-        view = self._scratch.local_bytes[: n * 4].view(torch.float32)
+        """Broadcast an ordinary CUDA tensor (any dtype, viewed as bytes) from ``root`` by staging it through
+        symmetric scratch: the root writes every peer's copy with the broadcast kernel (Horovod's
+        broadcast_global_variables role)."""
+        flat = tensor.reshape(-1).view(torch.uint8) if tensor.is_contiguous() else tensor.contiguous().reshape(-1).view(torch.uint8)
+        nb = flat.numel()
+        n = (nb + 15) // 16 * 16
+        sc = self._staging(n)
+        view = sc.local_bytes[:n]
         if self.rank == root:
-            view[: flat.numel()].copy_(flat)
-        self.broadcast_(self._scratch, 0, n, root)      # offsets are in fp32 elements of the scratch allocation
-        flat.copy_(view[: flat.numel()])
+            view[:nb].copy_(flat)
+        self.broadcast_(sc, 0, n // 4, root)            # offsets are in fp32 elements of the scratch allocation
+        if tensor.is_contiguous():
+            flat.copy_(view[:nb])
+        else:
+            tensor.copy_(view[:nb].view(tensor.dtype).view(tensor.shape))
         return tensor
+
+    def allgather_tensor(self, tensor: torch.Tensor) -> List[torch.Tensor]:
+        """All-gather equally sized CUDA tensors through symmetric scratch; returns one tensor per rank."""
+        flat = tensor.contiguous().reshape(-1).view(torch.uint8)
+        nb = flat.numel()
+        seg = (nb + 15) // 16 * 16
+        sc = self._staging(seg * self.world)
+        sc.local_bytes[self.rank * seg: self.rank * seg + nb].copy_(flat)
+        self.allgather_(sc, 0, seg // 4)
+        return [sc.local_bytes[r * seg: r * seg + nb].clone().view(tensor.dtype).view(tensor.shape)
+                for r in range(self.world)]
 
     def _count(self):
         self.launches += 1

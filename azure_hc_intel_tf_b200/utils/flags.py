@@ -82,8 +82,12 @@ class Params:
     # --- B200 additions
     fabric: str = "auto"
     kernels: str = "auto"
-    fusion_threshold: int = 0      # 0 → HOROVOD_FUSION_THRESHOLD env or 128 MiB
-    use_cuda_graph: bool = False
+    fusion_threshold: int = 0      # 0 → HOROVOD_FUSION_THRESHOLD env, else 16 MiB on fabric nvl / 128 MiB elsewhere
+    use_cuda_graph: Optional[bool] = None      # None → on for --kernels=b200 on a GPU (the measured configuration)
+    lr_schedule: str = "constant"  # constant | warmup_poly (LARS style) | piecewise (tf_cnn_benchmarks ResNet style)
+    num_learning_rate_warmup_epochs: float = 0.0
+    num_epochs_total: float = 90.0
+    horovod_timeline: Optional[str] = None     # filled from HOROVOD_TIMELINE
     lars: bool = False
     lars_eta: float = 0.001
     timeline: Optional[str] = None
@@ -131,7 +135,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--fabric", type=str, default=d.fabric, choices=FABRICS)
     p.add_argument("--kernels", type=str, default=d.kernels, choices=KERNELS)
     p.add_argument("--fusion_threshold", type=int, default=0)
-    p.add_argument("--use_cuda_graph", type=absl_bool, default=False, nargs="?", const=True)
+    p.add_argument("--use_cuda_graph", type=absl_bool, default=None, nargs="?", const=True)
+    p.add_argument("--lr_schedule", type=str, default=d.lr_schedule, choices=["constant", "warmup_poly", "piecewise"])
+    p.add_argument("--num_learning_rate_warmup_epochs", type=float, default=0.0)
+    p.add_argument("--num_epochs_total", type=float, default=d.num_epochs_total)
     p.add_argument("--lars", type=absl_bool, default=False, nargs="?", const=True)
     p.add_argument("--lars_eta", type=float, default=d.lars_eta)
     p.add_argument("--timeline", type=str, default=None)
@@ -139,19 +146,28 @@ def build_parser() -> argparse.ArgumentParser:
     return p
 
 
-def resolve_fusion_threshold(p: Params) -> int:
-    """--fusion_threshold, else HOROVOD_FUSION_THRESHOLD (run-tf-sing-ucx-openmpi.sh:105), else 128 MiB."""
+NVL_FUSION_THRESHOLD = 16 << 20
+
+
+def resolve_fusion_threshold(p: Params, fabric: Optional[str] = None) -> int:
+    """--fusion_threshold, else HOROVOD_FUSION_THRESHOLD (run-tf-sing-ucx-openmpi.sh:105), else the fabric's default:
+    Horovod's 128 MiB for the library fabrics (the reference's setting), 16 MiB on the NVLink fabric. There a bucket
+    costs one kernel launch and no negotiation, so buckets are sized by backward time rather than by message
+    overhead: ResNet-50's 102 MB of gradients become seven buckets and the first ones are reduced and applied while
+    the earlier layers are still in backward; with 128 MiB the whole model is ONE bucket that can only start after
+    the last gradient exists."""
     if p.fusion_threshold > 0:
         return p.fusion_threshold
     env = os.environ.get("HOROVOD_FUSION_THRESHOLD")
     if env:
         return int(env)
-    return 134217728
+    return NVL_FUSION_THRESHOLD if fabric == "nvl" else 134217728
 
 
 def parse(argv=None) -> Params:
     ns = build_parser().parse_args(argv)
     p = Params(**vars(ns))
+    p.horovod_timeline = os.environ.get("HOROVOD_TIMELINE") or None
     validate(p)
     return p
 

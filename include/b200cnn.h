@@ -32,10 +32,13 @@ const char* b200_last_error(void);
 /* Momentum SGD over a flat range of n elements (n % 1024 == 0):
  *   g' = grad*grad_scale + wd*decay[t]*w ; (LARS: g' *= trust[t]) ; m = mu*m + g' ; w -= lr*m ; shadow = bf16(w)
  * block_tensor[i] names the tensor owning elements [1024 i, 1024 i + 1024) or -1 for padding; it may be NULL
- * (then decay applies everywhere and trust is ignored). shadow may be NULL. (run-tf-sing-ucx-openmpi.sh:73) */
+ * (then decay applies everywhere and trust is ignored). shadow may be NULL. lr_dev (optional): device float that
+ * overrides `lr` at run time, so a learning-rate schedule works under a captured CUDA graph
+ * (run-tf-sing-ucx-openmpi.sh:73). */
 int b200_sgd_momentum_flat(float* master, float* mom, const float* grad, b200_bf16* shadow, int64_t n,
                            const int32_t* block_tensor, const float* tensor_decay, const float* tensor_lars,
-                           const float* trust, float lr, float mu, float wd, float grad_scale, void* stream);
+                           const float* trust, float lr, float mu, float wd, float grad_scale, const float* lr_dev,
+                           void* stream);
 
 /* LARS: per-tensor squared norms of w and grad*grad_scale over a flat range → norms[2t], norms[2t+1]
  * (norms must be zeroed by the caller), then trust[t] = eta*|w| / (|g| + wd*decay[t]*|w| + eps) for tensors

@@ -17,5 +17,6 @@
 set -e
 HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 export PYTHONPATH="${HERE}/..:${PYTHONPATH}"
-export HOROVOD_FUSION_THRESHOLD="${HOROVOD_FUSION_THRESHOLD:-134217728}"
+# HOROVOD_FUSION_THRESHOLD (the reference exports 134217728, :105) is honoured when set; unset, the launcher picks
+# 128 MiB for nccl/sock and 16 MiB for nvl (buckets that overlap with backward).
 exec python -m azure_hc_intel_tf_b200.parallel.launcher "$@"
