@@ -49,6 +49,9 @@ class BenchmarkCNN:
         if self.kernels == "b200" and not want_cuda:
             raise SystemExit("--kernels=b200 needs a B200; use --kernels=cudnn on CPU")
         self.dtype = torch.bfloat16 if (p.use_fp16 and want_cuda) else torch.float32
+        if self.kernels == "cudnn" and want_cuda:
+            # the stock-library path gets the library's own tuning: per-shape algorithm search instead of heuristics
+            torch.backends.cudnn.benchmark = True
         torch.manual_seed(p.seed)
         self.model = models.create_model(p.model, kernels=self.kernels)
         self.batch = p.batch_size or self.model.default_batch_size
@@ -104,7 +107,7 @@ class BenchmarkCNN:
             ps = [q for _, q in named]
             if p.optimizer in ("momentum", "sgd", "lars"):
                 opt = torch.optim.SGD(ps, lr=self.lr, momentum=0.0 if p.optimizer == "sgd" else p.momentum,
-                                      weight_decay=p.weight_decay)
+                                      weight_decay=p.weight_decay, **({"fused": True} if self.device.type == "cuda" else {}))
             elif p.optimizer == "rmsprop":
                 opt = torch.optim.RMSprop(ps, lr=self.lr, alpha=0.9, momentum=p.momentum, eps=1.0,
                                           weight_decay=p.weight_decay)
@@ -173,8 +176,12 @@ class BenchmarkCNN:
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
+            from ..ops import b200 as _b200ops
+            before = _b200ops.launch_count
             with torch.cuda.graph(g):
                 self._g_loss = self.train_step(self._g_images, self._g_labels)
+            # every launcher of ours ran exactly once during capture: that is the number of our kernels per replay
+            self.graph_launches = _b200ops.launch_count - before
             self._graph = g
         if images.data_ptr() != self._g_images.data_ptr():
             self._g_images.copy_(images, non_blocking=True)

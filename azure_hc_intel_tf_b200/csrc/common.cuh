@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <cstdio>
 
 #include "b200cnn.h"
@@ -33,6 +34,20 @@ void set_error(const char* fmt, ...);
 #define B200_LAUNCH_CHECK() B200_CUDA(cudaGetLastError())
 
 constexpr int kNumSMs = 148;
+
+// Kernel function attributes (the opt-in to more than 48 KiB of dynamic shared memory) are per DEVICE, so a "set it
+// once" flag has to be kept per device too: true the first time this is called for `seen` with the current device.
+inline bool first_use_on_device(std::atomic<uint64_t>& seen) {
+  int d = 0;
+  cudaGetDevice(&d);
+  const uint64_t bit = 1ull << (d & 63);
+  return (seen.fetch_or(bit) & bit) == 0;
+}
+
+// Dynamic shared memory the persistent tensor-core kernels may take: 223 of the SM's 228 KiB. The rest (and the
+// registers a 576-thread CTA leaves free) is the room in which a 128-thread communication CTA (csrc/comm) becomes
+// resident NEXT TO a convolution CTA, so gradient collectives progress under a running convolution.
+constexpr int kMaxConvSmem = 223 * 1024;
 
 // 8 bf16 values = one 16-byte vector.
 struct alignas(16) bf16x8 {

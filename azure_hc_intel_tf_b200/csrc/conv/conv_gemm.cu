@@ -717,11 +717,10 @@ int plan_grid(int num_m_tiles, int num_n_tiles, int ctas) {
 template <int kCtas, bool kHalo>
 cudaError_t launch_kernel(int grid, size_t smem, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb,
                           const CUtensorMap& mo, const GemmParams& p) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<kCtas, kHalo>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  static std::atomic<uint64_t> attr_set{0};
+  if (first_use_on_device(attr_set)) {
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel<kCtas, kHalo>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxConvSmem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid);
@@ -768,7 +767,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
     const int grid0 = plan_grid(p.num_m_tiles, p.num_n_tiles, p.ctas) / p.ctas;
     static const int res_max_kb = getenv("B200_CONV_BRES_KB") ? atoi(getenv("B200_CONV_BRES_KB")) : 96;
     // at least two 16 KiB activation stages must still fit next to the resident slice
-    const bool fits = fixed + bres_bytes + 2 * kABytes <= 227 * 1024;
+    const bool fits = fixed + bres_bytes + 2 * kABytes <= kMaxConvSmem;
     p.b_resident = (res_ok && fits && bres_bytes <= (int64_t)res_max_kb * 1024 && p.num_m_tiles >= 2 * kNumSMs &&
                     grid0 % p.num_n_tiles == 0) ? 1 : 0;
     if (p.b_resident) {
@@ -776,7 +775,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, cudaStre
       stage_bytes_eff = kABytes;
     }
   }
-  int stages = (227 * 1024 - fixed) / stage_bytes_eff;
+  int stages = (kMaxConvSmem - fixed) / stage_bytes_eff;
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   p.stages = stages;

@@ -522,11 +522,9 @@ static int wgrad_impl(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
   const int nb = (p.block_n + 63) / 64;
   const size_t smem = (size_t)p.stages * (p.halo ? 2 * kHaloBytes + nb * kDyTileBytes : p.T * 2 * kBox + nb * kBox) +
                       sizeof(WBarriers) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_set{0};
+  if (first_use_on_device(attr_set))
+    B200_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxConvSmem));
   const int grid = p.slices * p.m_groups * p.n_tiles;
   conv_wgrad_kernel<<<grid, kThreads, smem, st>>>(mx, mdy, p);
   B200_LAUNCH_CHECK();

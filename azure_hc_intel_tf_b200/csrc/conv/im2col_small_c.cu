@@ -104,11 +104,9 @@ extern "C" int b200_im2col_small_c(const b200_bf16* x, b200_bf16* a, const b200_
   const size_t smem = (size_t)g->r * span * 2;
   const int64_t blocks = (int64_t)g->n * pblocks * qblocks;
   const int threads = 256 / kvecs * kvecs;             // a whole number of pixels per pass
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<uint64_t> attr_set{0};
+  if (first_use_on_device(attr_set))
     B200_CUDA(cudaFuncSetAttribute(im2col_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmemElems * 2));
-    attr_set = true;
-  }
   im2col_kernel<<<(unsigned)blocks, threads, smem, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), a, *g, kdim, kpad, span, qblocks, qt);
   B200_LAUNCH_CHECK();

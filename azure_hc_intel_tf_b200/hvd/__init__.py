@@ -65,6 +65,8 @@ def init(fabric: str = "auto", device: Optional[str] = None, timeout_s: int = 60
         dist.init_process_group(backend, rank=rank, world_size=world,
                                 timeout=datetime.timedelta(seconds=timeout_s), **kw)
         _state["owns_pg"] = True
+    elif world > 1 and fabric in ("nvl", "nccl") and dist.get_backend() != "nccl":
+        raise RuntimeError(f"fabric {fabric} needs the existing process group to use the nccl backend")
     _state.update(init=True, fabric=fabric, rank=rank, world=world, local_rank=lrank,
                   local_size=_env_int("LOCAL_WORLD_SIZE", world))
     if fabric == "nvl" and world > 1:
@@ -72,15 +74,19 @@ def init(fabric: str = "auto", device: Optional[str] = None, timeout_s: int = 60
         _state["symm"] = symm.SymmetricContext.create(rank, world, _state["device"])
 
 
-def shutdown() -> None:
+def shutdown(keep_process_group: bool = False) -> None:
+    """Tear the runtime down. ``keep_process_group=True`` keeps the torch.distributed group alive so that a following
+    ``init(fabric=...)`` in the same process can switch fabrics (bench.py measures the stock arm and the product arm
+    back to back in one launch)."""
     if not _state["init"]:
         return
     if _state.get("symm") is not None:
         _state["symm"].close()
         _state["symm"] = None
-    if _state["owns_pg"] and dist.is_initialized():
+    if _state["owns_pg"] and dist.is_initialized() and not keep_process_group:
         dist.destroy_process_group()
-    _state.update(init=False, fabric=None, owns_pg=False)
+        _state["owns_pg"] = False
+    _state.update(init=False, fabric=None)
 
 
 def is_initialized() -> bool:

@@ -221,3 +221,148 @@ def w_nvl_fused_training(rank, world, steps, lars):
         opt.step()
     torch.cuda.synchronize()
     return [p.detach().cpu().contiguous() for p in net.parameters()], len(opt.plan.buckets), opt._symm is not None
+
+
+def w_nvl_fused_buckets(rank, world, sizes, algo, lars, rounds):
+    """Fused allreduce + update kernels on buckets far above the one-shot range (the sizes real models produce), with
+    one rank delayed on the device before every launch and no host synchronisation between buckets. Checks, per round:
+    every rank ends with bit-identical master / momentum / bf16 weights, and they match the unfused arithmetic
+    (gradients gathered with NCCL, summed in rank order in fp32, then the plain PyTorch update rule). ``sizes``:
+    tensor sizes in elements; the plan cuts them into buckets of ``sizes[0]`` elements' worth of bytes."""
+    import torch.distributed as dist
+    from .. import hvd
+    from ..parallel import symm as symm_mod
+    ctx = hvd.symmetric_context()
+    assert ctx is not None and hvd.fabric() == "nvl"
+    dev = hvd.device()
+    torch.manual_seed(99)
+    params = [(f"t{i}", torch.nn.Parameter(torch.randn(n, 1, device=dev) if i % 2 else torch.randn(n, device=dev)))
+              for i, n in enumerate(sizes)]
+    mk = hvd.LARS if lars else hvd.MomentumSGD
+    kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-3, lowp=True, fusion_threshold=max(sizes) * 4 // 2)
+    if lars:
+        kw["eta"] = 0.01
+    base = mk(params, **kw)
+    opt = hvd.DistributedOptimizer(base, named_parameters=params)
+    assert opt._symm is not None
+    ctx.algo = symm_mod.ALGOS[algo]
+    if algo == "nvls" and not getattr(opt._symm_grad, "mc_ptr", 0):
+        return "skip: no multicast mapping"
+    nb = len(base.plan.buckets)
+    assert nb >= 2, nb
+    scale = 1.0 / world
+    bad = []
+    for rnd in range(rounds):
+        g = torch.Generator(device="cpu").manual_seed(1000 * rnd + rank)
+        mine = torch.randn(base.total, generator=g).to(dev)
+        # elements that belong to no tensor (alignment padding, the tail of a tensor's last block) never receive a
+        # gradient in training: keep them zero here too
+        live = torch.zeros(base.total, dtype=torch.bool, device=dev)
+        for s0, n0 in base.ranges:
+            live[s0:s0 + n0] = True
+        mine[~live] = 0.0
+        # reference: what the update must produce
+        every = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        acc = every[0].clone()
+        for r in range(1, world):
+            acc += every[r]
+        acc *= scale
+        ref = mk([(n, torch.nn.Parameter(p.detach().clone())) for n, p in params], **kw)
+        ref.master.copy_(base.master)
+        ref.mom.copy_(base.mom)
+        ref.grad.copy_(acc)
+        ref.compute_trust()
+        ref._update_range_torch(0, ref.total, ref.lr, 0.9, 1e-3, 1.0)
+        base.grad.copy_(mine)
+        torch.cuda.synchronize()
+        dist.barrier()
+        for b in range(nb):
+            if rank == (rnd + b) % world:
+                torch.cuda._sleep(3_000_000)            # ~1.5 ms: this rank reaches the kernel late
+            lo, hi = base.bucket_range(b)
+            la = base.lars_bucket_args(b, ctx.block) if lars else None
+            ctx.fused_allreduce_sgd(opt._symm_grad, base, lo, hi, scale, lars=la)
+        torch.cuda.synchronize()
+        for name, t, r_t, tol in (("master", base.master, ref.master, 2e-5), ("mom", base.mom, ref.mom, 2e-5),
+                                  ("shadow", base.shadow.float(), ref.shadow.float(), 1e-2)):
+            peers = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(peers, t.contiguous())
+            if not all(torch.equal(peers[0], p) for p in peers[1:]):
+                bad.append((rnd, name, "ranks differ"))
+            if not torch.allclose(t, r_t, atol=tol, rtol=tol):
+                where = [(i, n, round(float((t[s0:s0 + n] - r_t[s0:s0 + n]).abs().max()), 6))
+                         for i, (s0, n) in enumerate(base.ranges)
+                         if not torch.allclose(t[s0:s0 + n], r_t[s0:s0 + n], atol=tol, rtol=tol)]
+                bad.append((rnd, name, "mismatch vs unfused", where,
+                            [round(float(x), 6) for x in base.trust], [round(float(x), 6) for x in ref.trust]))
+    ctx.algo = symm_mod.ALGO_AUTO
+    return bad
+
+
+def w_nvl_misc(rank, world):
+    """All-gather, point-to-point probes, sub-block allreduce and the host-level hvd collectives on the nvl fabric."""
+    from .. import hvd
+    ctx = hvd.symmetric_context()
+    dev = hvd.device()
+    bad = []
+    # all-gather kernel, plain and multicast-capable buffers
+    for mc in (False, True):
+        n = 4096 + 8
+        buf = ctx.alloc_like_flat(n * world, torch.float32, multicast=mc)
+        buf.local.fill_(-1.0)
+        buf.local[rank * n:(rank + 1) * n] = torch.arange(n, device=dev, dtype=torch.float32) + 1000.0 * rank
+        torch.cuda.synchronize()
+        hvd.barrier()
+        ctx.allgather_(buf, 0, n)
+        torch.cuda.synchronize()
+        want = torch.cat([torch.arange(n, device=dev, dtype=torch.float32) + 1000.0 * r for r in range(world)])
+        if not torch.equal(buf.local, want):
+            bad.append(("allgather", mc))
+    # allreduce below one block (1 KiB and 16 bytes): the one-shot kernel masks the tail
+    buf = ctx.alloc_like_flat(4096, torch.float32)
+    for n in (4, 256, 1000, 1024 + 512):
+        buf.local.fill_(7.0)
+        buf.local[:n] = float(rank + 1)
+        torch.cuda.synchronize()
+        hvd.barrier()
+        ctx.allreduce_range_(buf, 0, n, 1.0)
+        torch.cuda.synchronize()
+        tot = float(sum(range(1, world + 1)))
+        if not (bool((buf.local[:n] == tot).all()) and bool((buf.local[n:] == 7.0).all())):
+            bad.append(("small allreduce", n))
+    # point-to-point: rank 0 pushes to / pulls from rank 1; ping-pong latency probe
+    big = ctx.alloc_like_flat(1 << 20, torch.float32)
+    big.local.fill_(float(rank))
+    torch.cuda.synchronize()
+    hvd.barrier()
+    if rank == 0:
+        big.local[:4096] = 42.0
+        ctx.p2p_copy(big, 1, 0, 4096, pull=False)
+        ctx.p2p_copy(big, 1, 8192, 4096, pull=True)
+        torch.cuda.synchronize()
+    hvd.barrier()
+    if rank == 1 and not bool((big.local[:4096] == 42.0).all()):
+        bad.append(("p2p push",))
+    if rank == 0 and not bool((big.local[8192:8192 + 4096] == 1.0).all()):
+        bad.append(("p2p pull",))
+    out = torch.zeros(2, device=dev)
+    for a, b in ((0, 1), (1, 0), (0, world - 1)):
+        if a == b:
+            continue
+        ctx.p2p_pingpong(big, a, b, 256, 50, out)
+        torch.cuda.synchronize()
+        if rank == a and not (0.2 < float(out[0]) < 1000.0):
+            bad.append(("pingpong", a, b, float(out[0])))
+    # host-level API
+    g = hvd.allgather(torch.full((rank + 1, 3), float(rank), device=dev))
+    if g.shape[0] != sum(range(1, world + 1)) or float(g[-1, 0]) != float(world - 1):
+        bad.append(("hvd.allgather",))
+    t = torch.arange(10, device=dev, dtype=torch.int64) * (rank + 1)
+    hvd.broadcast_(t, root_rank=world - 1)
+    if not torch.equal(t, torch.arange(10, device=dev, dtype=torch.int64) * world):
+        bad.append(("hvd.broadcast_ int64",))
+    obj = hvd.broadcast_object({"rank": rank, "x": [1, 2, 3]}, 0)
+    if obj != {"rank": 0, "x": [1, 2, 3]}:
+        bad.append(("broadcast_object", obj))
+    return bad

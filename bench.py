@@ -14,10 +14,14 @@ BASELINE.json configs[1]):
   already lives on the device, CUDA-event timed, barrier + synchronize on both sides, MAX over ranks.
 * ``e2e``    — the same steps through the public API (``BenchmarkCNN.step``) with the batch copied from pinned
   host memory every step (uint8 NHWC images + int64 labels) and the loss read back to the host every step.
+* ``baseline_same_run`` — the stock-library arm (PyTorch + cuDNN with benchmark-mode algorithm search, bf16 autocast,
+  channels_last, fused SGD, whole-step CUDA graph, NCCL bucketed allreduce) measured by the same code for the same
+  steps on the same GPUs right before the product arm; ``vs_baseline`` is value ÷ that number. The reference itself
+  publishes no number and cannot be installed, so this same-run stock arm is the bar.
 
-Impl arms: ``b200`` = this framework's kernels and NVLink fabric; ``baseline`` = stock PyTorch/cuDNN + NCCL
-(BASELINE.md §3); ``reference`` = the unmodified reference from baseline/_ref — it is a set of shell
-installers with no Python package and cannot be installed offline, so that arm reports ``unavailable``.
+Impl arms: ``b200`` = this framework's kernels and NVLink fabric; ``baseline`` = the stock arm alone;
+``reference`` = the unmodified reference from baseline/_ref — it is a set of shell installers with no Python
+package and cannot be installed offline, so that arm reports ``unavailable``.
 """
 from __future__ import annotations
 
@@ -47,17 +51,20 @@ def reference_arm() -> int:
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons (B200_PROFILING.md recipe), sampled every 50 ms by one background
+    process. ``window()`` brackets a timed region; ``summary(name)`` reports the median over the samples taken INSIDE
+    that region only (an idle GPU sits at a low clock, so samples from set-up time say nothing about the run)."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int = 0, period_ms: int = 200):
+    def __init__(self, gpu_index: int = 0, period_ms: int = 50):
         self.proc = None
-        self.lines = []
+        self.lines = []          # (host time, csv line)
         self.gpu = gpu_index
         self.period = period_ms
+        self.windows = {}
 
     def start(self):
         try:
@@ -71,18 +78,34 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
 
-    def stop(self) -> dict:
+    def begin(self, name: str):
+        self.windows[name] = [time.perf_counter(), None]
+
+    def end(self, name: str):
+        self.windows[name][1] = time.perf_counter()
+
+    def stop(self):
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
+
+    def summary(self, name: str) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t0, t1 = self.windows.get(name, (0.0, None))
+        t1 = t1 if t1 is not None else time.perf_counter()
         sm, mx, pw, reasons = [], [], [], set()
-        for ln in self.lines:
+        for ts, ln in list(self.lines):
+            # a sample describes the interval that ended when it was printed: keep those printed inside the window
+            # (plus one period of slack at the end, the sampler's own latency)
+            if not (t0 + self.period / 2e3 <= ts <= t1 + self.period / 1e3):
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -90,12 +113,13 @@ class ClockSampler:
                 sm.append(float(f[1])), mx.append(float(f[2])), pw.append(float(f[3]))
             except ValueError:
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+            for rname, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
                 if v.lower().startswith("active"):
-                    reasons.add(name)
+                    reasons.add(rname)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "window_s": round(t1 - t0, 3),
+                "reasons": sorted(reasons)}
 
 
 def main() -> int:
@@ -110,8 +134,9 @@ def main() -> int:
     ap.add_argument("--kernels", default=None)
     ap.add_argument("--optimizer", default="momentum")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the same-run stock arm (vs_baseline becomes null)")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
-                    help="capture the whole training step in a CUDA graph (auto: on for the b200 arm)")
+                    help="capture the whole training step in a CUDA graph (auto: on for both arms)")
     a = ap.parse_args()
     if a.impl == "reference":
         return reference_arm()
@@ -122,6 +147,7 @@ def main() -> int:
     import torch.distributed as dist
     from azure_hc_intel_tf_b200 import hvd
     from azure_hc_intel_tf_b200.cli.cnn_benchmarks import BenchmarkCNN
+    from azure_hc_intel_tf_b200.ops import b200 as b200ops, conv_impl
     from azure_hc_intel_tf_b200.utils import flags
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -129,102 +155,121 @@ def main() -> int:
     if world != a.gpus and rank == 0 and world > 1:
         print(f"note: --gpus {a.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
     n = world
-    if a.impl == "baseline":
-        kernels, fabric = a.kernels or "cudnn", a.fabric or "nccl"
-    else:
-        kernels, fabric = a.kernels or "b200", a.fabric or ("nvl" if n > 1 else "auto")
-    argv = [f"--model={a.model}", f"--batch_size={a.batch}", f"--num_batches={a.steps}",
-            f"--num_warmup_batches={a.warmup}", "--variable_update=horovod", f"--optimizer={a.optimizer}",
-            "--device=gpu", f"--kernels={kernels}", f"--fabric={fabric}", "--use_fp16=True"]
-    use_graph = a.cuda_graph == "on" or (a.cuda_graph == "auto" and a.impl == "b200")
-    argv.append(f"--use_cuda_graph={use_graph}")
-
-    def measure(source: str, read_loss: bool):
-        """Returns (seconds for K steps on this rank, launches of our kernels, last loss, bench)."""
-        p = flags.parse(argv)
-        b = BenchmarkCNN(p, data_source=source)
-        from azure_hc_intel_tf_b200.ops import b200 as b200ops
-        launches_per_step = None
-        if use_graph:
-            # the first graph-mode call runs eager steps and captures; count our launches in one eager step first
-            b.p.use_cuda_graph = False
-            b.step()
-            b200ops.launch_count = 0
-            b.step()
-            launches_per_step = b200ops.launch_count
-            b.p.use_cuda_graph = True
-        for _ in range(a.warmup):
-            loss = b.step()
-            if read_loss:
-                loss.item()
-        torch.cuda.synchronize()
-        if n > 1:
-            hvd.barrier()
-        torch.cuda.synchronize()
-        b200ops.launch_count = 0
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
-        e0.record()
-        last = None
-        for _ in range(a.steps):
-            loss = b.step()
-            if read_loss:
-                last = loss.item()          # device→host read of the step's result, every step
-        e1.record()
-        torch.cuda.synchronize()
-        wall = time.perf_counter() - t0
-        if n > 1:
-            hvd.barrier()
-        torch.cuda.synchronize()
-        secs = e0.elapsed_time(e1) / 1e3
-        if not read_loss:
-            last = float(loss.item())
-        launches = b200ops.launch_count if launches_per_step is None else launches_per_step * a.steps
-        t = torch.tensor([secs, wall], dtype=torch.float64, device="cuda")
-        if n > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]), float(t[1]), launches, last, b
-
+    global_batch = a.batch * n
     sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
     if rank == 0:
         sampler.start()
-    secs, _wall, launches, loss_v, b = measure("device", read_loss=False)
-    clocks = sampler.stop() if rank == 0 else None
-    from azure_hc_intel_tf_b200.ops import conv_impl
-    paths = dict(conv_impl.path_counts)
-    global_batch = a.batch * n
-    value = a.steps * global_batch / secs
-    fabric_used, kernels_used = b.fabric, b.kernels
-    e2e = None
-    if not a.no_e2e:
+
+    def run_arm(impl: str, e2e: bool) -> dict:
+        if impl == "baseline":
+            kernels, fabric = a.kernels if a.impl == "baseline" and a.kernels else "cudnn", \
+                              a.fabric if a.impl == "baseline" and a.fabric else "nccl"
+        else:
+            kernels, fabric = a.kernels or "b200", a.fabric or ("nvl" if n > 1 else "auto")
+        use_graph = a.cuda_graph != "off"
+        if impl == "baseline" and n > 1 and os.environ.get("B200_BASELINE_GRAPH", "1") == "0":
+            use_graph = False
+        argv = [f"--model={a.model}", f"--batch_size={a.batch}", f"--num_batches={a.steps}",
+                f"--num_warmup_batches={a.warmup}", "--variable_update=horovod", f"--optimizer={a.optimizer}",
+                "--device=gpu", f"--kernels={kernels}", f"--fabric={fabric}", "--use_fp16=True",
+                f"--use_cuda_graph={use_graph}"]
+
+        def measure(source: str, read_loss: bool, tag: str):
+            """K timed steps on this rank → (device seconds, wall seconds, launches of our kernels, last loss, bench)."""
+            b = BenchmarkCNN(flags.parse(argv), data_source=source)
+            for _ in range(a.warmup + (4 if use_graph else 0)):     # graph mode: three eager steps + the capture first
+                loss = b.step()
+                if read_loss:
+                    loss.item()
+            torch.cuda.synchronize()
+            if n > 1:
+                hvd.barrier()
+            torch.cuda.synchronize()
+            b200ops.launch_count = 0
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if rank == 0:
+                sampler.begin(tag)
+            t0 = time.perf_counter()
+            e0.record()
+            last = None
+            for _ in range(a.steps):
+                loss = b.step()
+                if read_loss:
+                    last = loss.item()          # device→host read of the step's result, every step
+            e1.record()
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+            if rank == 0:
+                sampler.end(tag)
+            if n > 1:
+                hvd.barrier()
+            torch.cuda.synchronize()
+            secs = e0.elapsed_time(e1) / 1e3
+            if not read_loss:
+                last = float(loss.item())
+            # graph mode: the kernels of ours that one replay launches were counted during capture (every launcher ran
+            # exactly once then); eager mode: counted live
+            per_replay = getattr(b, "graph_launches", None)
+            launches = per_replay * a.steps if (b.use_graph and per_replay is not None) else b200ops.launch_count
+            t = torch.tensor([secs, wall], dtype=torch.float64, device="cuda")
+            if n > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t[0]), float(t[1]), launches, last, b
+
+        conv_impl.path_counts.clear()
+        secs, _wall, launches, loss_v, b = measure("device", False, impl)
+        out = {"impl": impl, "value": round(a.steps * global_batch / secs, 2), "ms_per_step": round(1e3 * secs / a.steps, 3),
+               "fabric": b.fabric, "kernels": b.kernels, "cuda_graph": bool(b.use_graph),
+               "conv_paths": dict(conv_impl.path_counts), "gpu_launches": launches, "final_loss": loss_v,
+               "fusion_buckets": len(b.opt.plan.buckets) if hasattr(b.opt, "plan") else None,
+               "clocks": sampler.summary(impl) if rank == 0 else None}
         del b
         torch.cuda.empty_cache()
-        esecs, ewall, _l, _loss, b2 = measure("host", read_loss=True)
-        e2e = {"value": a.steps * global_batch / max(esecs, ewall), "unit": "images/sec",
-               "h2d_bytes_per_step": int(b2.data.h2d_bytes) * n, "d2h_bytes_per_step": 4 * n,
-               "ms_per_step": 1e3 * max(esecs, ewall) / a.steps,
-               "input": "uint8 NHWC images + int64 labels from pinned host memory, loss.item() every step"}
+        if e2e:
+            esecs, ewall, _l, _loss, b2 = measure("host", True, impl + "_e2e")
+            out["e2e"] = {"value": a.steps * global_batch / max(esecs, ewall), "unit": "images/sec",
+                          "h2d_bytes_per_step": int(b2.data.h2d_bytes) * n, "d2h_bytes_per_step": 4 * n,
+                          "ms_per_step": 1e3 * max(esecs, ewall) / a.steps,
+                          "input": "uint8 NHWC images + int64 labels from pinned host memory, loss.item() every step"}
+            del b2
+            torch.cuda.empty_cache()
+        hvd.shutdown(keep_process_group=True)
+        return out
+
     base = None
-    try:
-        with open(os.path.join(ROOT, "baseline", "measured.json")) as f:
-            base = json.load(f).get(a.model, {}).get(str(n))
-    except Exception:
-        base = None
+    if a.impl == "b200" and not a.no_baseline:
+        try:
+            base = run_arm("baseline", e2e=not a.no_e2e)
+        except Exception as e:      # the stock arm must never take the product number down with it
+            base = {"impl": "baseline", "error": f"{e.__class__.__name__}: {e}"}
+            try:
+                hvd.shutdown(keep_process_group=True)
+            except Exception:
+                pass
+    res = run_arm(a.impl, e2e=not a.no_e2e)
+    sampler.stop()
     if rank == 0:
-        out = {"metric": f"{a.model} synthetic ImageNet training images/sec", "value": round(value, 2),
+        base_v = base.get("value") if base else None
+        out = {"metric": f"{a.model} synthetic ImageNet training images/sec", "value": res["value"],
                "unit": "images/sec", "n_gpus": n, "steps": a.steps, "warmup": a.warmup,
-               "ms_per_step": round(1e3 * secs / a.steps, 3), "higher_is_better": True, "scaling": "weak",
-               "vs_baseline": round(value / base, 4) if base else None, "dtype": "bf16", "data": "synthetic",
+               "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": round(res["value"] / base_v, 4) if base_v else None, "dtype": "bf16", "data": "synthetic",
                "impl": a.impl,
                "config": {"model": a.model, "global_batch": global_batch, "per_gpu_batch": a.batch,
                           "image_size": 224 if "inception" not in a.model else 299, "num_classes": 1001,
-                          "optimizer": a.optimizer, "parallelism": f"dp{n}", "fabric": fabric_used,
-                          "kernels": kernels_used, "conv_paths": paths, "cuda_graph": bool(use_graph),
+                          "optimizer": a.optimizer, "parallelism": f"dp{n}", "fabric": res["fabric"],
+                          "kernels": res["kernels"], "conv_paths": res["conv_paths"], "cuda_graph": res["cuda_graph"],
+                          "fusion_buckets": res["fusion_buckets"],
                           "l2": "no flush: each step streams >10 GB of activations, far larger than the 126 MB L2",
-                          "timing": "CUDA events on the compute stream, barrier+synchronize both sides, max over ranks"},
-               "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": loss_v}
+                          "timing": "CUDA events on the compute stream, barrier+synchronize both sides, max over ranks",
+                          "vs_baseline_is": "value / baseline_same_run.value (stock PyTorch+cuDNN+NCCL arm, tuned, same "
+                                            "run, same GPUs); the reference publishes no number"},
+               "clocks": res["clocks"], "e2e": res.get("e2e"), "gpu_launches": res["gpu_launches"],
+               "final_loss": res["final_loss"], "baseline_same_run": base}
         print(json.dumps(out), flush=True)
     hvd.shutdown()
+    if dist.is_initialized():
+        dist.destroy_process_group()
     return 0
 
 
