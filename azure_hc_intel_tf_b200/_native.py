@@ -35,6 +35,7 @@ def _declare_host(lib):
     vp, i32, i64, dbl, cp = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_char_p
     sig = {
         "hvd_plan_create": (vp, [C.POINTER(TensorDesc), i32, i64, i32]),
+        "hvd_plan_create_tail": (vp, [C.POINTER(TensorDesc), i32, i64, i32, i64]),
         "hvd_plan_destroy": (None, [vp]),
         "hvd_plan_num_buckets": (i32, [vp]),
         "hvd_plan_num_segments": (i32, [vp]),

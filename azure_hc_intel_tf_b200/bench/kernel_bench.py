@@ -44,7 +44,7 @@ def flush_l2():
     _flush.zero_()
 
 
-def timeit(fn, iters=5, warmup=2):
+def timeit(fn, iters=5, warmup=3):
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
@@ -67,7 +67,11 @@ def main(argv=None):
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--json", default=None)
     ap.add_argument("--no-lib", action="store_true")
+    ap.add_argument("--no-cudnn-benchmark", action="store_true",
+                    help="leave cuDNN on its heuristics (default: benchmark mode, i.e. per-shape algorithm search - the "
+                         "library column is then the library at its best)")
     a = ap.parse_args(argv)
+    torch.backends.cudnn.benchmark = not a.no_cudnn_benchmark
     tf_peak, hbm, src = peaks()
     net = models.create_model(a.model, kernels="b200")
     layers = OrderedDict()

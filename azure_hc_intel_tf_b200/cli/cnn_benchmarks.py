@@ -97,7 +97,8 @@ class BenchmarkCNN:
             mu = 0.0 if p.optimizer == "sgd" else p.momentum
             opt = hvd.MomentumSGD(named, lr=self.lr, momentum=mu, weight_decay=p.weight_decay,
                                   lars=p.optimizer == "lars", lars_eta=p.lars_eta,
-                                  lowp=self.kernels == "b200", fusion_threshold=thr)
+                                  lowp=self.kernels == "b200", fusion_threshold=thr,
+                                  fusion_tail=flags_mod.resolve_fusion_tail(self.fabric if self.world > 1 else None))
             if p.lr_schedule != "constant" or p.num_learning_rate_warmup_epochs > 0:
                 n_img = 50000 if p.data_name == "cifar10" else lr_schedule.IMAGENET_TRAIN
                 opt.lr_schedule = lr_schedule.make(p.lr_schedule, self.lr, self.global_batch,

@@ -189,6 +189,57 @@ __device__ __forceinline__ void sgd_apply_block(const SgdDev& sgd, const float4 
   }
 }
 
+// Four blocks per trip: all twelve loads (gradient, master, momentum) are issued before the first use, so a thread has
+// twelve 16-byte requests in flight instead of three. `gb[u] < 0` marks an empty slot.
+__device__ __forceinline__ void sgd_apply_blocks4(const SgdDev& sgd, const float* g, const int64_t gb[4], int tid, float lr) {
+  float4 gv[4], wv[4], mv[4];
+  float dec[4], tr[4];
+  bool live[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    live[u] = gb[u] >= 0;
+    dec[u] = sgd.wd;
+    tr[u] = 1.0f;
+    if (live[u] && sgd.block_tensor) {
+      const int t = sgd.block_tensor[(gb[u] * kBlock) >> 10];
+      if (t < 0) {
+        live[u] = false;
+      } else {
+        dec[u] = sgd.wd * sgd.tdecay[t];
+        if (sgd.trust && sgd.tlars[t] != 0.0f) tr[u] = sgd.trust[t];
+      }
+    }
+    if (live[u]) {
+      const int64_t i = gb[u] * kBlock + tid * 4;
+      gv[u] = ld_peer_f4(g + i);
+      wv[u] = *reinterpret_cast<const float4*>(sgd.master + i);
+      mv[u] = *reinterpret_cast<const float4*>(sgd.mom + i);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (!live[u]) continue;
+    const int64_t i = gb[u] * kBlock + tid * 4;
+    float ww[4] = {wv[u].x, wv[u].y, wv[u].z, wv[u].w}, mm[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w};
+    const float gg[4] = {gv[u].x, gv[u].y, gv[u].z, gv[u].w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float ge = (gg[k] + dec[u] * ww[k]) * tr[u];
+      mm[k] = sgd.mu * mm[k] + ge;
+      ww[k] -= lr * mm[k];
+    }
+    *reinterpret_cast<float4*>(sgd.master + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+    *reinterpret_cast<float4*>(sgd.mom + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    if (sgd.shadow) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
+      uint2 pk;
+      pk.x = *reinterpret_cast<uint32_t*>(&lo);
+      pk.y = *reinterpret_cast<uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(sgd.shadow + i) = pk;
+    }
+  }
+}
+
 // Sum over the CTA of two per-thread values, in a fixed order (warp tree, then warps 0..7 in sequence).
 __device__ __forceinline__ float2 cta_sum2(float a, float b, float (*red)[8]) {
   a = warp_sum(a);
@@ -209,9 +260,11 @@ __device__ __forceinline__ float2 cta_sum2(float a, float b, float (*red)[8]) {
   return make_float2(sa, sb);
 }
 
-template <bool kNvls, bool kLars>
-__global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int64_t offset, int64_t nblk, float scale,
-                                                                 SgdDev sgd) {
+// kW: compile-time bound on the rank count (2, 4 or 8) so the two-shot loop can keep 8 / kW owned blocks x kW peers =
+// eight peer loads in flight per thread in registers. <= 80 registers x 128 threads: see the note at kThreads.
+template <bool kNvls, bool kLars, int kW>
+__global__ void __launch_bounds__(kThreads, 6) allreduce_f32_kernel(CommDev c, int64_t offset, int64_t nblk, float scale,
+                                                                    SgdDev sgd) {
   __shared__ uint32_t s_epoch;
   __shared__ float s_red[2][8];
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
@@ -223,7 +276,6 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
   for (int64_t j = blockIdx.x;; j += gridDim.x) {
     const int64_t b = j * c.world + c.rank;
     if (b >= nblk) break;
-    const int64_t off = offset + b * kBlock + tid * 4;
     if (kNvls) {
       // NVLS: one load returns the sum over all ranks' copies, computed inside the NVSwitch; one store lands in
       // every rank's copy. Link traffic per GPU: S/N reduced in + S/N out, instead of (N-1)/N*S each way.
@@ -250,26 +302,42 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
       j += 3 * (int64_t)gridDim.x;      // the loop header advances by one more gridDim.x
       continue;
     }
-    float4 v[B200_COMM_MAX_RANKS];
+    // Peer loads are latency-bound (about 2 us each over NVLink), so a thread keeps eight of them in flight: with
+    // two ranks it takes four owned blocks per trip, with up to four ranks two, with more one.
+    constexpr int kU = 8 / kW;
+    float4 v[kU][kW];
 #pragma unroll
-    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) v[p] = ld_peer_f4(reinterpret_cast<const float*>(c.buf[p]) + off);
-    float4 acc = v[0];
+    for (int u = 0; u < kU; ++u) {
+      const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
+      if (bu < nblk) {
 #pragma unroll
-    for (int p = 1; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) {
-        acc.x += v[p].x;
-        acc.y += v[p].y;
-        acc.z += v[p].z;
-        acc.w += v[p].w;
+        for (int p = 0; p < kW; ++p)
+          if (p < c.world) v[u][p] = ld_peer_f4(reinterpret_cast<const float*>(c.buf[p]) + offset + bu * kBlock + tid * 4);
       }
-    acc.x *= scale;
-    acc.y *= scale;
-    acc.z *= scale;
-    acc.w *= scale;
+    }
 #pragma unroll
-    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) st_peer_f4(reinterpret_cast<float*>(c.buf[p]) + off, acc);
+    for (int u = 0; u < kU; ++u) {
+      const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
+      if (bu < nblk) {
+        float4 acc = v[u][0];
+#pragma unroll
+        for (int p = 1; p < kW; ++p)
+          if (p < c.world) {
+            acc.x += v[u][p].x;
+            acc.y += v[u][p].y;
+            acc.z += v[u][p].z;
+            acc.w += v[u][p].w;
+          }
+        acc.x *= scale;
+        acc.y *= scale;
+        acc.z *= scale;
+        acc.w *= scale;
+#pragma unroll
+        for (int p = 0; p < kW; ++p)
+          if (p < c.world) st_peer_f4(reinterpret_cast<float*>(c.buf[p]) + offset + bu * kBlock + tid * 4, acc);
+      }
+    }
+    j += (int64_t)(kU - 1) * gridDim.x;      // the loop header advances by one more gridDim.x
   }
   cta_barrier_all_ranks(c, &s_epoch);
 
@@ -279,18 +347,18 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
     const float lr = sgd.lr_dev ? __ldg(sgd.lr_dev) : sgd.lr;
     if (!kLars) {
       // exactly the blocks this CTA's barrier covers: j in {blockIdx.x + k*gridDim.x}, all owners p of that j
-      for (int64_t j = blockIdx.x; j * c.world < nblk; j += gridDim.x) {
-        float4 gv[B200_COMM_MAX_RANKS];
+      // item q of this CTA = block (blockIdx.x + (q / world) * gridDim.x) * world + q % world; four items per trip
+      const int64_t base_blk = offset / kBlock;
+      for (int64_t q = 0;; q += 4) {
+        if ((blockIdx.x + (q / c.world) * (int64_t)gridDim.x) * c.world >= nblk) break;
+        int64_t gb[4];
 #pragma unroll
-        for (int p = 0; p < B200_COMM_MAX_RANKS; ++p) {
-          const int64_t b = j * c.world + p;
-          if (p < c.world && b < nblk) gv[p] = ld_peer_f4(g + offset + b * kBlock + tid * 4);
+        for (int u = 0; u < 4; ++u) {
+          const int64_t qq = q + u;
+          const int64_t b = (blockIdx.x + (qq / c.world) * (int64_t)gridDim.x) * c.world + qq % c.world;
+          gb[u] = b < nblk ? base_blk + b : -1;
         }
-#pragma unroll
-        for (int p = 0; p < B200_COMM_MAX_RANKS; ++p) {
-          const int64_t b = j * c.world + p;
-          if (p < c.world && b < nblk) sgd_apply_block(sgd, gv[p], offset / kBlock + b, tid, lr);
-        }
+        sgd_apply_blocks4(sgd, g, gb, tid, lr);
       }
     } else {
       // (1) per-block partial norms of this bucket's blocks (any CTA may take any block after the grid barrier...
@@ -332,8 +400,15 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_kernel(CommDev c, int6
       }
       grid_barrier_local(c);
       // (3) update the blocks of those tensors (the range may reach back into an earlier bucket)
-      for (int64_t gb = sgd.upd_lo + blockIdx.x; gb < sgd.upd_hi; gb += gridDim.x)
-        sgd_apply_block(sgd, ld_peer_f4(g + gb * kBlock + tid * 4), gb, tid, lr);
+      for (int64_t gb0 = sgd.upd_lo + blockIdx.x; gb0 < sgd.upd_hi; gb0 += 4 * (int64_t)gridDim.x) {
+        int64_t gb[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t x = gb0 + (int64_t)u * gridDim.x;
+          gb[u] = x < sgd.upd_hi ? x : -1;
+        }
+        sgd_apply_blocks4(sgd, g, gb, tid, lr);
+      }
     }
   }
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
@@ -689,10 +764,21 @@ int b200_allreduce_f32(const b200_comm* comm, int64_t offset, int64_t n, float s
   bool nvls = comm->mc != 0 && (algo == B200_COMM_ALGO_NVLS ||
                                 (algo == B200_COMM_ALGO_AUTO && comm->nvls_min_bytes >= 0 && n * 4 >= comm->nvls_min_bytes));
   B200_CHECK_ARG(algo != B200_COMM_ALGO_NVLS || nvls, "allreduce_f32: NVLS requested but the buffer has no multicast mapping");
-  if (nvls && lars) allreduce_f32_kernel<true, true><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
-  else if (nvls) allreduce_f32_kernel<true, false><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
-  else if (lars) allreduce_f32_kernel<false, true><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
-  else allreduce_f32_kernel<false, false><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s);
+#define B200_AR_LAUNCH(NVLS, LARS, W) allreduce_f32_kernel<NVLS, LARS, W><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale, s)
+  if (nvls) {
+    if (lars) B200_AR_LAUNCH(true, true, 8);
+    else B200_AR_LAUNCH(true, false, 8);
+  } else if (d.world <= 2) {
+    if (lars) B200_AR_LAUNCH(false, true, 2);
+    else B200_AR_LAUNCH(false, false, 2);
+  } else if (d.world <= 4) {
+    if (lars) B200_AR_LAUNCH(false, true, 4);
+    else B200_AR_LAUNCH(false, false, 4);
+  } else {
+    if (lars) B200_AR_LAUNCH(false, true, 8);
+    else B200_AR_LAUNCH(false, false, 8);
+  }
+#undef B200_AR_LAUNCH
   B200_LAUNCH_CHECK();
   return 0;
 }

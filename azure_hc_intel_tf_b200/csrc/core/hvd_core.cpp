@@ -36,12 +36,24 @@ extern "C" {
 
 hvd_plan* hvd_plan_create(const hvd_tensor_desc* tensors, int32_t n, int64_t threshold_bytes,
                           int32_t align_elems) {
+  return hvd_plan_create_tail(tensors, n, threshold_bytes, align_elems, 0);
+}
+
+hvd_plan* hvd_plan_create_tail(const hvd_tensor_desc* tensors, int32_t n, int64_t threshold_bytes,
+                               int32_t align_elems, int64_t tail_bytes) {
   if (n < 0 || (n > 0 && tensors == nullptr)) return nullptr;
   if (align_elems <= 0 || (align_elems & (align_elems - 1)) != 0) return nullptr;
   if (threshold_bytes <= 0) threshold_bytes = 134217728;  // reference default, 128 MiB
   auto* p = new hvd_plan();
   p->num_tensors = n;
   p->segments_per_tensor.assign(n, 0);
+
+  // The last bucket's collective cannot overlap with anything (backward is over when its final gradient lands), so
+  // its size is pure exposed time: with tail_bytes > 0 the tensors that make up the last tail_bytes of the gradient
+  // stream are cut off into a bucket of their own, however much room the open bucket still has.
+  int64_t total_bytes = 0, seen_bytes = 0;
+  for (int32_t t = 0; t < n; ++t) total_bytes += tensors[t].numel * tensors[t].elem_size;
+  bool tail_cut = tail_bytes <= 0;
 
   int32_t open = -1;  // index of the bucket currently being filled
   auto open_bucket = [&](int32_t elem_size, int32_t dtype_id) {
@@ -65,10 +77,17 @@ hvd_plan* hvd_plan_create(const hvd_tensor_desc* tensors, int32_t n, int64_t thr
     int64_t cap = threshold_bytes / d.elem_size / align_elems * align_elems;
     if (cap < align_elems) cap = align_elems;
     int64_t done = 0;
+    bool cut_here = false;
+    if (!tail_cut && open >= 0 && p->buckets[open].numel > 0 && total_bytes - seen_bytes <= tail_bytes) {
+      cut_here = true;
+      tail_cut = true;
+    }
+    seen_bytes += d.numel * d.elem_size;
     while (done < d.numel) {
       int64_t remaining = d.numel - done;
-      bool need_new = open < 0 || p->buckets[open].dtype_id != d.dtype_id ||
+      bool need_new = open < 0 || cut_here || p->buckets[open].dtype_id != d.dtype_id ||
                       p->buckets[open].elem_size != d.elem_size;
+      cut_here = false;
       if (!need_new) {
         int64_t room = cap - p->buckets[open].numel;
         // A tensor that fits a fresh bucket is never split just to top up the open one

@@ -39,7 +39,8 @@ class Buck:
 
 class FusionPlan:
     def __init__(self, numels: Sequence[int], elem_sizes: Sequence[int], dtype_ids: Sequence[int],
-                 flags: Sequence[int], threshold_bytes: int = DEFAULT_THRESHOLD, align_elems: int = ALIGN_ELEMS):
+                 flags: Sequence[int], threshold_bytes: int = DEFAULT_THRESHOLD, align_elems: int = ALIGN_ELEMS,
+                 tail_bytes: int = 0):
         lib = _native.host()
         n = len(numels)
         arr = (_native.TensorDesc * max(n, 1))()
@@ -47,7 +48,7 @@ class FusionPlan:
             arr[i].numel, arr[i].elem_size, arr[i].dtype_id, arr[i].flags = \
                 int(numels[i]), int(elem_sizes[i]), int(dtype_ids[i]), int(flags[i])
         self._lib = lib
-        self._h = lib.hvd_plan_create(arr, n, int(threshold_bytes), int(align_elems))
+        self._h = lib.hvd_plan_create_tail(arr, n, int(threshold_bytes), int(align_elems), int(tail_bytes))
         if not self._h:
             raise ValueError("fusion planner rejected its input")
         self.num_tensors = n

@@ -53,7 +53,7 @@ class MomentumSGD:
 
     def __init__(self, params: Iterable, lr: float, momentum: float = 0.9, weight_decay: float = 0.0,
                  lars: bool = False, lars_eta: float = 0.001, lars_eps: float = 1e-9, lowp: bool = False,
-                 fusion_threshold: int = DEFAULT_THRESHOLD, grad_alloc=None):
+                 fusion_threshold: int = DEFAULT_THRESHOLD, grad_alloc=None, fusion_tail: int = 0):
         named = []
         for i, p in enumerate(params):
             if isinstance(p, tuple):
@@ -79,7 +79,7 @@ class MomentumSGD:
             flags.append(f)
         self.flags = flags
         self.plan = FusionPlan([p.numel() for p in self.params], [4] * len(self.params), [0] * len(self.params),
-                               flags, fusion_threshold, ALIGN_ELEMS)
+                               flags, fusion_threshold, ALIGN_ELEMS, fusion_tail)
         total = self.plan.total_elems[0]
         self.total = total
         self.master = torch.zeros(total, dtype=torch.float32, device=dev)

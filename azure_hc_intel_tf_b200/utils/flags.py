@@ -164,6 +164,16 @@ def resolve_fusion_threshold(p: Params, fabric: Optional[str] = None) -> int:
     return NVL_FUSION_THRESHOLD if fabric == "nvl" else 134217728
 
 
+def resolve_fusion_tail(fabric: Optional[str] = None) -> int:
+    """Bytes of the gradient stream's END that get a bucket of their own (B200_FUSION_TAIL; default 1 MiB on the NVLink
+    fabric, 0 = Horovod's plain greedy fill elsewhere). The last bucket's collective runs after backward has ended,
+    so whatever it takes is exposed: ResNet-50's last megabyte is conv0 + the first residual block."""
+    env = os.environ.get("B200_FUSION_TAIL")
+    if env not in (None, ""):
+        return int(env)
+    return (1 << 20) if fabric == "nvl" else 0
+
+
 def parse(argv=None) -> Params:
     ns = build_parser().parse_args(argv)
     p = Params(**vars(ns))

@@ -54,6 +54,10 @@ typedef struct hvd_plan hvd_plan;
  * two. A tensor larger than the threshold is split into threshold-sized chunks (VGG-16 fc6). */
 hvd_plan* hvd_plan_create(const hvd_tensor_desc* tensors, int32_t n, int64_t threshold_bytes,
                           int32_t align_elems);
+/* The same, with the tensors that make up the last `tail_bytes` of the gradient stream cut off into a bucket of their
+ * own: the final bucket's collective is the only one that cannot overlap with backward, so it is kept small. */
+hvd_plan* hvd_plan_create_tail(const hvd_tensor_desc* tensors, int32_t n, int64_t threshold_bytes,
+                               int32_t align_elems, int64_t tail_bytes);
 void hvd_plan_destroy(hvd_plan* p);
 int32_t hvd_plan_num_buckets(const hvd_plan* p);
 int32_t hvd_plan_num_segments(const hvd_plan* p);

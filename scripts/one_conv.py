@@ -15,13 +15,16 @@ m.pad = ((pd, pd), (pd, pd)); m.out_hw = ((h + 2 * pd - k) // stride + 1,) * 2
 x = torch.randn(n, h, h, cin, device="cuda").bfloat16().permute(0, 3, 1, 2)
 w = torch.randn(cout, k, k, cin, device="cuda").bfloat16().permute(0, 3, 1, 2)
 dy = torch.randn(n, m.out_hw[0], m.out_hw[1], cout, device="cuda").bfloat16().permute(0, 3, 1, 2)
+ONLY = os.environ.get("ONLY", "")          # fprop | dgrad | wgrad: run just that kernel (ncu capture target)
 for _ in range(3):
-    y, st = conv_umma.fprop(x, w, m, want_stats=WS)
-    if conv_umma.supports_dgrad(dy, w, m, x.shape):
+    if ONLY in ("", "fprop"):
+        y, st = conv_umma.fprop(x, w, m, want_stats=WS)
+    if ONLY in ("", "dgrad") and conv_umma.supports_dgrad(dy, w, m, x.shape):
         dx = conv_umma.dgrad(dy, w, m, x.shape)
-    dw = conv_umma.wgrad(x, dy, m)
+    if ONLY in ("", "wgrad"):
+        dw = conv_umma.wgrad(x, dy, m)
 torch.cuda.synchronize()
-print("ok", y.shape, dw.shape)
+print("ok")
 if len(sys.argv) > 7 and sys.argv[7] == "prof":
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as pr:

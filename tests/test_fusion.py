@@ -87,3 +87,23 @@ def test_tracker_counts_down_and_rearms():
     assert tr.oldest_inflight_seconds() == 0.0
     tr.begin_step()
     assert tr.pending() == 2 and tr.ready(0) == []
+
+
+def test_tail_bucket_is_cut_at_a_tensor_boundary():
+    """The last bucket's collective cannot overlap with backward, so the planner can cut the end of the gradient
+    stream off into a small bucket of its own (fabric nvl default: 1 MiB)."""
+    from azure_hc_intel_tf_b200.hvd.fusion import FusionPlan
+    numels = [1000, 5000, 300000, 2000000, 100000, 64, 9408]
+    plain = FusionPlan(numels, [4] * 7, [0] * 7, [1] * 7, 4 << 20, 1024, 0)
+    tail = FusionPlan(numels, [4] * 7, [0] * 7, [1] * 7, 4 << 20, 1024, 1 << 20)
+    assert len(tail.buckets) == len(plain.buckets) + 1
+    last = tail.buckets[-1]
+    segs = [s for s in tail.segments if s.bucket == len(tail.buckets) - 1]
+    assert [s.tensor for s in segs] == [4, 5, 6] and all(s.tensor_offset == 0 for s in segs)
+    assert last.numel * 4 <= 1 << 20
+    assert tail.total_elems[0] >= plain.total_elems[0]
+    # every tensor is still one contiguous range of the flat buffer
+    for t in range(7):
+        _, start, n = tail.tensor_range(t)
+        assert n == numels[t] and start % 1024 == 0
+    assert tail.hash != plain.hash
