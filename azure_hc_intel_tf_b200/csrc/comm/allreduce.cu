@@ -64,7 +64,9 @@ constexpr uint64_t kWatchdogNs = 30000000000ull;   // 30 s: a peer never arrived
 
 // All threads of the CTA call this. s_epoch is a shared-memory word holding this CTA's last used epoch.
 __device__ __forceinline__ void cta_barrier_all_ranks(const CommDev& c, uint32_t* s_epoch) {
-  __threadfence_system();          // this thread's peer stores are performed before the CTA signals
+  // Every thread's peer stores happen-before the bar.sync; the release stores below are cumulative over what their
+  // threads observed through that barrier, so the data is visible to a peer that acquires the flag (the PTX release
+  // pattern; one fence per signalling thread instead of one per thread of the CTA).
   __syncthreads();
   const uint32_t e = *s_epoch + 1;
   if ((int)threadIdx.x < c.world) {
@@ -457,41 +459,55 @@ __global__ void __launch_bounds__(kThreads) allreduce_f32_oneshot_kernel(CommDev
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
 }
 
-// bf16 payload: 1024 elements per block (128 threads x 8), fp32 accumulation, one rounding.
-__global__ void __launch_bounds__(kThreads) allreduce_bf16_kernel(CommDev c, int64_t offset, int64_t nblk, float scale) {
+// bf16 payload: 1024 elements per block (128 threads x 8), fp32 accumulation, one rounding. Same eight-loads-in-flight
+// structure as the fp32 two-shot loop (kW = compile-time bound on the rank count).
+template <int kW>
+__global__ void __launch_bounds__(kThreads, 6) allreduce_bf16_kernel(CommDev c, int64_t offset, int64_t nblk, float scale) {
   __shared__ uint32_t s_epoch;
   if (threadIdx.x == 0) s_epoch = *epoch_slot(c);
   __syncthreads();
   cta_barrier_all_ranks(c, &s_epoch);
   const int tid = threadIdx.x;
-  for (int64_t j = blockIdx.x;; j += gridDim.x) {
-    const int64_t b = j * c.world + c.rank;
-    if (b >= nblk) break;
-    const int64_t off = offset + b * kBlockBf16 + tid * 8;
-    float acc[8];
+  constexpr int kU = 8 / kW;
+  for (int64_t j = blockIdx.x;; j += (int64_t)kU * gridDim.x) {
+    if (j * c.world + c.rank >= nblk) break;
+    float4 raw[kU][kW];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
-    bf16x8 v[B200_COMM_MAX_RANKS];
+    for (int u = 0; u < kU; ++u) {
+      const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
+      if (bu < nblk) {
 #pragma unroll
-    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) {
-        float4 raw = ld_peer_f4(reinterpret_cast<const float*>(reinterpret_cast<const b200_bf16*>(c.buf[p]) + off));
-        v[p] = *reinterpret_cast<bf16x8*>(&raw);
+        for (int p = 0; p < kW; ++p)
+          if (p < c.world)
+            raw[u][p] = ld_peer_f4(reinterpret_cast<const float*>(reinterpret_cast<const b200_bf16*>(c.buf[p]) + offset +
+                                                                  bu * kBlockBf16 + tid * 8));
       }
+    }
 #pragma unroll
-    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) {
-        float f[8];
-        unpack8(v[p], f);
+    for (int u = 0; u < kU; ++u) {
+      const int64_t bu = (j + (int64_t)u * gridDim.x) * c.world + c.rank;
+      if (bu < nblk) {
+        float acc[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] += f[k];
+        for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+#pragma unroll
+        for (int p = 0; p < kW; ++p)
+          if (p < c.world) {
+            float f[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(&raw[u][p]), f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += f[k];
+          }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] *= scale;
+        const bf16x8 out = pack8(acc);
+        const float4 o4 = *reinterpret_cast<const float4*>(&out);
+#pragma unroll
+        for (int p = 0; p < kW; ++p)
+          if (p < c.world)
+            st_peer_f4(reinterpret_cast<float*>(reinterpret_cast<b200_bf16*>(c.buf[p]) + offset + bu * kBlockBf16 + tid * 8), o4);
       }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] *= scale;
-    const bf16x8 out = pack8(acc);
-#pragma unroll
-    for (int p = 0; p < B200_COMM_MAX_RANKS; ++p)
-      if (p < c.world) st8(reinterpret_cast<b200_bf16*>(c.buf[p]) + off, out);
+    }
   }
   cta_barrier_all_ranks(c, &s_epoch);
   if (threadIdx.x == 0) *epoch_slot(c) = s_epoch;
@@ -509,16 +525,17 @@ __global__ void __launch_bounds__(kThreads) barrier_kernel(CommDev c) {
 // store for all of them). `skip` = a rank that needs no copy (the source's own buffer), -1 = none.
 __device__ __forceinline__ void push_to_peers(const CommDev& c, const float* src, int64_t offset, int64_t nvec) {
   const int64_t stride = (int64_t)gridDim.x * kThreads;
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 4 * stride) {
-    float4 v[4];
+  const bool mc = c.mc != 0 && c.world > 2;      // with two ranks a plain peer store is the same traffic, minus the echo
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 8 * stride) {
+    float4 v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (i + u * stride < nvec) v[u] = *reinterpret_cast<const float4*>(src + (i + u * stride) * 4);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       const int64_t e = i + u * stride;
       if (e >= nvec) continue;
-      if (c.mc) {
+      if (mc) {
         asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(
                          reinterpret_cast<float*>(c.mc) + offset + e * 4),
                      "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w)
@@ -561,13 +578,14 @@ __global__ void __launch_bounds__(kThreads) p2p_copy_kernel(CommDev c, int peer,
   const float* src = reinterpret_cast<const float*>(c.buf[pull ? peer : c.rank]) + offset;
   float* dst = reinterpret_cast<float*>(c.buf[pull ? c.rank : peer]) + offset;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 4 * stride) {
-    float4 v[4];
+  // eight 16-byte requests in flight per thread: a pull has to cover ~2 us of NVLink round trip at ~770 GB/s
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += 8 * stride) {
+    float4 v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (i + u * stride < nvec) v[u] = ld_peer_f4(src + (i + u * stride) * 4);
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (i + u * stride < nvec) st_peer_f4(dst + (i + u * stride) * 4, v[u]);
   }
 }
@@ -592,8 +610,7 @@ __global__ void __launch_bounds__(kThreads) p2p_pingpong_kernel(CommDev c, int a
   float acc = 0.0f;
   auto send = [&]() {
     for (int i = threadIdx.x; i < nvec; i += kThreads) st_peer_f4(theirs + i * 4, make_float4(acc, 1.f, 2.f, 3.f));
-    __threadfence_system();
-    __syncthreads();
+    __syncthreads();                 // the release store of thread 0 below is cumulative over the CTA's payload stores
     ++seq;
     if (threadIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flag), "r"(seq) : "memory");
   };
@@ -791,7 +808,10 @@ int b200_allreduce_bf16(const b200_comm* comm, int64_t offset, int64_t n, float 
                  "allreduce_bf16: offset and n must be multiples of 2048 elements");
   const int64_t nblk = n / kBlockBf16;
   ctas = ctas_for((nblk + d.world - 1) / d.world, ctas);
-  allreduce_bf16_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, nblk, scale);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (d.world <= 2) allreduce_bf16_kernel<2><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale);
+  else if (d.world <= 4) allreduce_bf16_kernel<4><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale);
+  else allreduce_bf16_kernel<8><<<ctas, kThreads, 0, st>>>(d, offset, nblk, scale);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -811,7 +831,7 @@ int b200_broadcast_f32(const b200_comm* comm, int64_t offset, int64_t n, int32_t
   if (int e = to_dev(comm, d, ctas)) return e;
   B200_CHECK_ARG(n > 0 && n % 4 == 0 && offset >= 0 && offset % 4 == 0 && root >= 0 && root < d.world,
                  "broadcast_f32: n and offset must be multiples of 4, root in range");
-  ctas = ctas_for(n / kBlock, ctas);
+  ctas = ctas_for(n / kBlock, B200_COMM_MAX_CTAS);
   broadcast_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, n / 4, root);
   B200_LAUNCH_CHECK();
   return 0;
@@ -823,7 +843,7 @@ int b200_allgather_f32(const b200_comm* comm, int64_t offset, int64_t n_per_rank
   if (int e = to_dev(comm, d, ctas)) return e;
   B200_CHECK_ARG(n_per_rank > 0 && n_per_rank % 4 == 0 && offset >= 0 && offset % 4 == 0,
                  "allgather_f32: n_per_rank and offset must be multiples of 4 elements");
-  ctas = ctas_for(n_per_rank / kBlock, ctas);
+  ctas = ctas_for(n_per_rank / kBlock, B200_COMM_MAX_CTAS);
   allgather_f32_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, offset, n_per_rank / 4);
   B200_LAUNCH_CHECK();
   return 0;
@@ -835,7 +855,7 @@ int b200_p2p_copy(const b200_comm* comm, int32_t peer, int64_t offset, int64_t n
   if (int e = to_dev(comm, d, ctas)) return e;
   B200_CHECK_ARG(peer >= 0 && peer < d.world && peer != d.rank && n > 0 && n % 4 == 0 && offset >= 0 && offset % 4 == 0,
                  "p2p_copy: peer must be another rank; n and offset multiples of 4 elements");
-  ctas = ctas_for(n / kBlock, ctas);
+  ctas = ctas_for(n / kBlock, B200_COMM_MAX_CTAS);
   p2p_copy_kernel<<<ctas, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d, peer, offset, n / 4, pull);
   B200_LAUNCH_CHECK();
   return 0;

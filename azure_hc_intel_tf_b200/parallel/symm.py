@@ -66,6 +66,21 @@ def _declare(lib):
     lib.b200_symm_open_handle.argtypes, lib.b200_symm_open_handle.restype = [vp, C.POINTER(vp)], i32
     lib.b200_symm_close_handle.argtypes, lib.b200_symm_close_handle.restype = [vp], i32
     lib.b200_comm_pad_bytes.argtypes, lib.b200_comm_pad_bytes.restype = [], i64
+    lib.b200_vmm_supported.argtypes, lib.b200_vmm_supported.restype = [i32, C.POINTER(i32)], i32
+    lib.b200_vmm_create.argtypes = [i64, i32, i32, i32, C.POINTER(vp), C.POINTER(i32), C.POINTER(i64)]
+    lib.b200_vmm_create.restype = i32
+    lib.b200_vmm_map_peer.argtypes, lib.b200_vmm_map_peer.restype = [vp, i32, i32], i32
+    lib.b200_vmm_ptr.argtypes, lib.b200_vmm_ptr.restype = [vp, i32], C.c_uint64
+    lib.b200_vmm_mc_create.argtypes, lib.b200_vmm_mc_create.restype = [vp, C.POINTER(i32)], i32
+    lib.b200_vmm_mc_import.argtypes, lib.b200_vmm_mc_import.restype = [vp, i32], i32
+    lib.b200_vmm_mc_add_device.argtypes, lib.b200_vmm_mc_add_device.restype = [vp], i32
+    lib.b200_vmm_mc_bind.argtypes, lib.b200_vmm_mc_bind.restype = [vp], i32
+    lib.b200_vmm_mc_ptr.argtypes, lib.b200_vmm_mc_ptr.restype = [vp], C.c_uint64
+    lib.b200_vmm_free.argtypes, lib.b200_vmm_free.restype = [vp], i32
+    lib.b200_fd_listen.argtypes, lib.b200_fd_listen.restype = [C.c_char_p], i32
+    lib.b200_fd_send.argtypes, lib.b200_fd_send.restype = [i32, C.c_char_p, i32, i32], i32
+    lib.b200_fd_recv.argtypes, lib.b200_fd_recv.restype = [i32, C.POINTER(i32)], i32
+    lib.b200_fd_close.argtypes, lib.b200_fd_close.restype = [i32], i32
     lib.b200_comm_block_elems.argtypes, lib.b200_comm_block_elems.restype = [], i32
     lib.b200_allgather_f32.argtypes, lib.b200_allgather_f32.restype = [C.POINTER(CommStruct), i64, i64, vp], i32
     lib.b200_p2p_copy.argtypes, lib.b200_p2p_copy.restype = [C.POINTER(CommStruct), i32, i64, i64, i32, vp], i32
@@ -120,25 +135,70 @@ class SymmBuffer:
             self.ptr = 0
 
 
-class McSymmBuffer:
-    """Symmetric allocation that also has a multicast (NVLS) mapping. The VMM allocation, the handle exchange and
-    the multicast binding are done by ``torch.distributed._symmetric_memory`` (allocation plumbing only: every
-    kernel that touches the memory is this framework's)."""
+class VmmSymmBuffer:
+    """Symmetric allocation on the CUDA virtual-memory-management API, optionally with a multicast (NVLS) mapping —
+    this framework's own allocator (csrc/comm/symm_alloc.cpp): cuMemCreate per rank, POSIX file descriptors passed
+    between the processes over abstract Unix-domain sockets, every peer mapped locally, and one multicast object that
+    all ranks bind their allocation to. ``torch.distributed`` only provides the barriers between the steps."""
 
-    def __init__(self, ctx: "SymmetricContext", nbytes: int, dtype: torch.dtype):
-        import torch.distributed._symmetric_memory as symm_mem
+    def __init__(self, ctx: "SymmetricContext", nbytes: int, dtype: torch.dtype, multicast: bool):
+        lib, world, rank = ctx.lib, ctx.world, ctx.rank
         self.ctx = ctx
+        h, fd, padded = C.c_void_p(), C.c_int32(-1), C.c_int64(0)
+        _check(lib.b200_vmm_create(nbytes, world, rank, int(multicast), C.byref(h), C.byref(fd), C.byref(padded)), "vmm_create")
+        self._h = h
         self.nbytes = nbytes
-        self.local_bytes = symm_mem.empty(nbytes, dtype=torch.uint8, device=ctx.device)
-        self.local_bytes.zero_()
-        self._hdl = symm_mem.rendezvous(self.local_bytes, dist.group.WORLD)
-        self.peers = [int(p) for p in self._hdl.buffer_ptrs]
-        self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
-        self.ptr = self.local_bytes.data_ptr()
+        ctx.vmm_seq += 1
+        name = lambda r: f"{ctx.sock_prefix}-{ctx.vmm_seq}-{r}".encode()
+        sock = lib.b200_fd_listen(name(rank))
+        if sock < 0:
+            raise RuntimeError(f"fd_listen failed: {lib.b200_last_error().decode()}")
+        try:
+            dist.barrier()                                   # every rank's socket is bound
+            for r in range(world):
+                if r != rank:
+                    _check(lib.b200_fd_send(sock, name(r), fd.value, rank), f"fd_send(rank {r})")
+            for _ in range(world - 1):
+                tag = C.c_int32(-1)
+                pfd = lib.b200_fd_recv(sock, C.byref(tag))
+                if pfd < 0:
+                    raise RuntimeError(f"fd_recv failed: {lib.b200_last_error().decode()}")
+                _check(lib.b200_vmm_map_peer(h, tag.value, pfd), f"vmm_map_peer(rank {tag.value})")
+                lib.b200_fd_close(pfd)
+            lib.b200_fd_close(fd.value)
+            dist.barrier()                                   # all peer descriptors consumed
+            self.mc_ptr = 0
+            if multicast:
+                if rank == 0:
+                    mfd = C.c_int32(-1)
+                    _check(lib.b200_vmm_mc_create(h, C.byref(mfd)), "vmm_mc_create")
+                    for r in range(1, world):
+                        _check(lib.b200_fd_send(sock, name(r), mfd.value, 1000), f"fd_send(multicast, rank {r})")
+                    lib.b200_fd_close(mfd.value)
+                else:
+                    tag = C.c_int32(-1)
+                    mfd = lib.b200_fd_recv(sock, C.byref(tag))
+                    if mfd < 0 or tag.value != 1000:
+                        raise RuntimeError(f"multicast descriptor not received: {lib.b200_last_error().decode()}")
+                    _check(lib.b200_vmm_mc_import(h, mfd), "vmm_mc_import")
+                    lib.b200_fd_close(mfd)
+                _check(lib.b200_vmm_mc_add_device(h), "vmm_mc_add_device")
+                dist.barrier()                               # every device is in the group before anyone binds
+                _check(lib.b200_vmm_mc_bind(h), "vmm_mc_bind")
+                dist.barrier()
+                self.mc_ptr = int(lib.b200_vmm_mc_ptr(h))
+        finally:
+            lib.b200_fd_close(sock)
+        self.peers = [int(lib.b200_vmm_ptr(h, r)) for r in range(world)]
+        self.ptr = self.peers[rank]
+        self._keep = _DevArray(self.ptr, nbytes)
+        self.local_bytes = torch.as_tensor(self._keep, device=ctx.device)
         self.local = self.local_bytes.view(dtype)
 
     def close(self):
-        self._hdl = None
+        if self._h is not None:
+            self.ctx.lib.b200_vmm_free(self._h)
+            self._h = None
 
 
 class SymmetricContext:
@@ -166,6 +226,11 @@ class SymmetricContext:
         self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(default_nvls)))
         self.algo = ALGOS[os.environ.get("B200_COMM_ALGO", "auto")]
         self.nvls_ok = None      # decided collectively at the first multicast allocation
+        self.vmm_seq = 0
+        pids = self.all_gather_bytes(torch.tensor([os.getpid() >> 24 & 255, os.getpid() >> 16 & 255, os.getpid() >> 8 & 255,
+                                                   os.getpid() & 255], dtype=torch.uint8))
+        pid0 = int.from_bytes(bytes(pids[0].tolist()), "big")
+        self.sock_prefix = f"b200vmm-{os.environ.get('MASTER_PORT', '0')}-{pid0}"
         self.stream = torch.cuda.Stream(device=device, priority=-1)
         self.buffers: List[SymmBuffer] = []
         self.pad = SymmBuffer(self, int(self.lib.b200_comm_pad_bytes()), torch.uint8)
@@ -189,23 +254,20 @@ class SymmetricContext:
         """Collective. ``multicast=True`` asks for a buffer with an NVLS multicast mapping and falls back to a plain
         IPC buffer (on every rank alike) if the platform refuses."""
         if multicast and self.nvls_ok is not False and os.environ.get("B200_COMM_MULTICAST", "1") != "0":
-            b, ok = None, 1
-            try:
-                b = McSymmBuffer(self, nbytes, dtype)
-                ok = 1 if b.mc_ptr else 0
-            except Exception as e:          # no VMM/multicast support on this platform
-                ok = 0
-                if self.rank == 0:
-                    print(f"[b200 comm] NVLS multicast unavailable ({e.__class__.__name__}: {e}); using P2P two-shot")
-            flag = torch.tensor([ok], device=self.device, dtype=torch.int32)
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            self.nvls_ok = bool(flag.item())
+            if self.nvls_ok is None:
+                # one collective decision, up front: VMM + POSIX descriptors + multicast on every rank's device
+                mc = C.c_int32(0)
+                vmm = self.lib.b200_vmm_supported(self.device.index or 0, C.byref(mc))
+                flag = torch.tensor([1 if (vmm == 1 and mc.value) else 0], device=self.device, dtype=torch.int32)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                self.nvls_ok = bool(flag.item())
+                if not self.nvls_ok and self.rank == 0:
+                    print("[b200 comm] NVLS multicast unavailable on this platform; using the P2P two-shot kernels")
             if self.nvls_ok:
+                b = VmmSymmBuffer(self, nbytes, dtype, multicast=True)
                 self.buffers.append(b)
                 dist.barrier()
                 return b
-            if b is not None:
-                b.close()
         b = SymmBuffer(self, nbytes, dtype)
         self.buffers.append(b)
         dist.barrier()           # every rank has mapped every peer before anyone launches a kernel on it

@@ -35,6 +35,30 @@ int b200_symm_free(void* dptr);
 int b200_symm_get_handle(void* dptr, void* handle_out /* 64 bytes */);
 int b200_symm_open_handle(const void* handle /* 64 bytes */, void** peer_ptr);
 int b200_symm_close_handle(void* peer_ptr);
+/* Symmetric memory on the virtual-memory-management API (csrc/comm/symm_alloc.cpp): the allocation that can carry an
+ * NVLS multicast mapping. Collective protocol, driven by the caller (parallel/symm.py does it with these calls and a
+ * barrier of its choice): every rank b200_vmm_create()s the same size and gets a POSIX file descriptor of its physical
+ * allocation; descriptors travel between processes over abstract Unix-domain sockets (b200_fd_listen / _send / _recv,
+ * SCM_RIGHTS); every rank b200_vmm_map_peer()s each peer's descriptor; for multicast rank 0 b200_vmm_mc_create()s and
+ * sends that descriptor, the others b200_vmm_mc_import() it, ALL b200_vmm_mc_add_device(), barrier, ALL
+ * b200_vmm_mc_bind(). b200_vmm_ptr(h, r) is rank r's buffer as mapped here, b200_vmm_mc_ptr(h) the multicast address.
+ * The reference's counterpart is MPI/UCX endpoint set-up (run-tf-sing-ucx-openmpi.sh:85-95). */
+int b200_vmm_supported(int32_t device, int32_t* multicast_ok);
+int b200_vmm_create(int64_t bytes, int32_t world, int32_t rank, int32_t want_multicast, void** handle_out, int32_t* fd_out,
+                    int64_t* padded_bytes);
+int b200_vmm_map_peer(void* handle, int32_t peer, int32_t fd);
+uint64_t b200_vmm_ptr(void* handle, int32_t rank);
+int b200_vmm_mc_create(void* handle, int32_t* fd_out);
+int b200_vmm_mc_import(void* handle, int32_t fd);
+int b200_vmm_mc_add_device(void* handle);
+int b200_vmm_mc_bind(void* handle);
+uint64_t b200_vmm_mc_ptr(void* handle);
+int b200_vmm_free(void* handle);
+int b200_fd_listen(const char* name);
+int b200_fd_send(int sock, const char* peer_name, int fd, int32_t tag);
+int b200_fd_recv(int sock, int32_t* tag_out);
+int b200_fd_close(int fd);
+
 /* Bytes of the per-rank signal pad (flags + epoch counters) the kernels need. */
 int64_t b200_comm_pad_bytes(void);
 /* Elements of one fp32 work block of the collectives (512): ownership in the two-shot algorithms alternates between
