@@ -55,6 +55,8 @@ OPTIONAL = {
     "b200_conv_stats_first_result_row": (i64, [C.POINTER(ConvGeom)]),
     "b200_gemm_stats_first_result_row": (i64, [i32, i32]),
     "b200_conv_dgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp]),
+    "b200_conv_dgrad_strided": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
+    "b200_conv_dgrad_strided_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_conv_wgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
     "b200_conv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_gemm_nt": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp]),

@@ -69,14 +69,21 @@ def stats_reduce(stats):
     return sums
 
 
+_ws = {}
+
+
 def dgrad(dy, w_lp, m, x_shape):
     g = geom(x_shape, m)
     dx = empty_nhwc(g.n, g.c, g.h, g.w, dy.device)
+    if lib().b200_conv_supported(C.byref(g), DGRAD) == 2:
+        # general strided filter: one stride-1 launch per stride phase (csrc/conv/conv_gemm.cu b200_conv_dgrad_strided)
+        ws = _workspace(lib().b200_conv_dgrad_strided_workspace_bytes(C.byref(g)), dy.device)
+        _check(lib().b200_conv_dgrad_strided(_ptr(dy), _ptr(w_lp), _ptr(dx), C.byref(g), _ptr(ws), _stream()),
+               "conv_dgrad_strided")
+        b200.count_launch(2 * m.stride[0] * m.stride[1] - 1)
+        return dx
     _check(lib().b200_conv_dgrad(_ptr(dy), _ptr(w_lp), _ptr(dx), C.byref(g), _stream()), "conv_dgrad")
     return dx
-
-
-_ws = {}
 
 
 def _workspace(need, device):

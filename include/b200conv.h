@@ -27,11 +27,12 @@ typedef struct b200_conv_geom {
 
 enum { B200_CONV_FPROP = 0, B200_CONV_DGRAD = 1, B200_CONV_WGRAD = 2 };
 
-/* 1 if the tensor-core kernel covers this geometry for `op`, else 0 (callers fall back to a library). */
+/* Non-zero if the tensor-core kernels cover this geometry for `op`, else 0 (callers fall back to a library). For
+ * B200_CONV_DGRAD the value says which entry point: 1 = b200_conv_dgrad, 2 = b200_conv_dgrad_strided. */
 int b200_conv_supported(const b200_conv_geom* g, int op);
 
-/* Smallest input-channel count b200_conv_supported accepts (default 64: thinner layers compute correctly through TMA
- * zero-fill but measured slower than the library; environment B200_CONV_MIN_C overrides, read once). */
+/* Smallest input-channel count b200_conv_supported accepts (default 8: thinner-than-64 layers run on the same kernels
+ * through TMA zero-fill; B200_CONV_MIN_C=64 hands them to the library, which measured faster on them; read once). */
 int b200_conv_min_channels(void);
 
 /* y[n,p,q,k] = sum_{r,s,c} x[n, p*sh - pad_t + r, q*sw - pad_l + s, c] * w[k,r,s,c].
@@ -47,6 +48,14 @@ int64_t b200_conv_stats_first_result_row(const b200_conv_geom* g);
 
 /* dx = gradient of fprop wrt x. Stride 1 (any filter), or strided 1x1 without padding. */
 int b200_conv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);
+
+/* dx for any other strided filter (3x3/2 of ResNet v1.5 and the Inception reductions, 7x7/2, ...), strides up to 4:
+ * one stride-1 tensor-core launch per stride phase (a, b) over the sub-filter w[:, a::sh, b::sw, :], whose rows the
+ * epilogue scatters to every sh-th / sw-th pixel of dx - no zero-upsampled copy of dy and no wasted MMAs.
+ * `workspace` (b200_conv_dgrad_strided_workspace_bytes) holds the packed sub-filter of the phase in flight. */
+int b200_conv_dgrad_strided(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* workspace,
+                            void* stream);
+int64_t b200_conv_dgrad_strided_workspace_bytes(const b200_conv_geom* g);
 
 /* dw[k,r,s,c] (fp32) = sum over pixels of dy[.,k] * x[window]. dw is overwritten. The pixel range is split over
  * CTAs; with `workspace` of b200_conv_wgrad_workspace_bytes(g) bytes the per-slice partials are folded in a fixed

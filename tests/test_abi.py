@@ -70,6 +70,7 @@ FPROP, DGRAD, WGRAD = 0, 1, 2
 def test_conv_support_matrix():
     lib = _cuda_lib()
     ok = lambda g, op: bool(lib.b200_conv_supported(C.byref(g), op))
+    code = lambda g, op: int(lib.b200_conv_supported(C.byref(g), op))
     # ResNet / VGG body layers: everything on the tensor-core path
     for g in (_geom(256, 56, 56, 64, 256, 1, 1, 1, 0), _geom(256, 56, 56, 64, 64, 3, 3, 1, 1),
               _geom(64, 224, 224, 64, 64, 3, 3, 1, 1), _geom(256, 7, 7, 512, 2048, 1, 1, 1, 0)):
@@ -79,12 +80,14 @@ def test_conv_support_matrix():
     assert ok(thin, FPROP) and ok(thin, DGRAD) and ok(thin, WGRAD)
     assert ok(_geom(128, 14, 14, 512, 24, 1, 1, 1, 0), FPROP)
     assert not ok(_geom(128, 14, 14, 512, 20, 1, 1, 1, 0), FPROP)
-    # thin input side after the first layer: left to the library by default (measured slower here)
+    # thin input side after the first layer (Inception stem): on the same kernels through TMA zero-fill
     stem = _geom(128, 149, 149, 32, 32, 3, 3, 1, 0)
-    assert not ok(stem, FPROP) and not ok(stem, WGRAD) and not ok(stem, DGRAD)
-    # strided dgrad: 1x1 only
-    assert ok(_geom(256, 56, 56, 256, 512, 1, 1, 2, 0), DGRAD)
-    assert not ok(_geom(256, 28, 28, 128, 128, 3, 3, 2, 1), DGRAD)
+    assert ok(stem, FPROP) and ok(stem, WGRAD) and ok(stem, DGRAD)
+    assert lib.b200_conv_min_channels() == 8
+    # strided dgrad: unpadded 1x1 in one launch (1), every other strided filter by stride phases (2)
+    assert code(_geom(256, 56, 56, 256, 512, 1, 1, 2, 0), DGRAD) == 1
+    assert code(_geom(256, 28, 28, 128, 128, 3, 3, 2, 1), DGRAD) == 2
+    assert code(_geom(256, 56, 56, 64, 64, 3, 3, 1, 1), DGRAD) == 1
     assert ok(_geom(256, 28, 28, 128, 128, 3, 3, 2, 1), FPROP) and ok(_geom(256, 28, 28, 128, 128, 3, 3, 2, 1), WGRAD)
 
 

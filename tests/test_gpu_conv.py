@@ -61,6 +61,11 @@ CASES = [
     (2, 35, 35, 192, 48, 1, 1, ((0, 0), (0, 0))),       # Inception-v3 5x5 reduce
     (2, 28, 28, 192, 16, 1, 1, ((0, 0), (0, 0))),       # GoogLeNet 5x5 reduce
     (2, 14, 14, 512, 24, 1, 1, ((0, 0), (0, 0))),       # GoogLeNet: Cout % 16 != 0
+    # thin input side (fewer than 64 input channels, not the first layer): half-empty k-blocks through TMA zero-fill
+    (2, 149, 149, 32, 32, 3, 1, ((0, 0), (0, 0))),      # Inception-v3 stem Conv2d_2a
+    (2, 147, 147, 32, 64, 3, 1, ((1, 1), (1, 1))),      # Inception-v3 stem Conv2d_2b
+    (2, 35, 35, 48, 64, 5, 1, ((2, 2), (2, 2))),        # Inception-v3 5x5 branch
+    (2, 28, 28, 16, 32, 5, 1, ((2, 2), (2, 2))),        # GoogLeNet 5x5 branch
     # CTA-pair (cta_group::2) mode with an odd number of 128-row tiles: the last pair's second CTA has no rows
     (3, 14, 14, 512, 256, 1, 1, ((0, 0), (0, 0))),      # fprop in pair mode (8 k-blocks, 256-wide tile), 5 M tiles
     (3, 14, 14, 256, 512, 1, 1, ((0, 0), (0, 0))),      # dgrad in pair mode, 5 M tiles
@@ -84,14 +89,26 @@ def test_fprop(n, h, w, cin, cout, k, stride, pad):
     assert torch.allclose(sums[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=1e-3)
 
 
-@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad", CASES)
+STRIDED_DGRAD = [
+    # general strided filters: one stride-1 launch per stride phase (b200_conv_dgrad_strided)
+    (2, 56, 56, 128, 128, 3, 2, ((0, 1), (0, 1))),      # TF 'SAME' on an even size: asymmetric padding
+    (2, 35, 35, 288, 384, 3, 2, ((0, 0), (0, 0))),      # Inception-v3 Mixed_6a reduction (VALID)
+    (2, 17, 17, 192, 320, 3, 2, ((0, 0), (0, 0))),      # Inception-v3 Mixed_7a
+    (2, 27, 27, 64, 192, 5, 2, ((2, 2), (2, 2))),       # 5x5 / 2
+    (2, 30, 30, 64, 64, 7, 2, ((3, 3), (3, 3))),        # 7x7 / 2 with 64 input channels
+    (2, 20, 20, 64, 128, 3, 3, ((1, 1), (1, 1))),       # stride 3: nine phases, some with a single tap
+    (2, 16, 16, 64, 128, 1, 2, ((1, 1), (1, 1))),       # padded strided 1x1: three of four phases have no tap (zeros)
+    (2, 14, 14, 256, 256, (3, 1), 2, ((1, 1), (0, 0))),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad", CASES + STRIDED_DGRAD)
 def test_dgrad(n, h, w, cin, cout, k, stride, pad):
     from azure_hc_intel_tf_b200.ops import conv_umma
     m = M(cin, cout, k, stride, pad, (h, w))
     x, wt = rnd((n, h, w, cin), 1), wrnd(cout, cin, m.k[0], m.k[1], 2)
     dy = rnd((n, m.out_hw[0], m.out_hw[1], cout), 3)
-    if not conv_umma.supports_dgrad(dy, wt, m, x.shape):
-        pytest.skip("geometry not covered by the tensor-core dgrad (library fallback is used)")
+    assert conv_umma.supports_dgrad(dy, wt, m, x.shape)
     dx = conv_umma.dgrad(dy, wt, m, x.shape)
     torch.cuda.synchronize()
     xf = x.float().requires_grad_()
