@@ -56,3 +56,32 @@ def test_trace_graph_and_tfprof_files_ws2_cpu(tmp_path):
     g = open(graph).read()
     assert "v0/cg/conv0/conv2d/kernel HWIO (32, 3, 5, 5) trainable" in g and "v0/cg/affine1/weights IO" in g
     assert "# trainable parameters:" in g
+
+
+def test_horovod_timeline_env_writes_bucket_events_ws2_cpu(tmp_path, monkeypatch):
+    """HOROVOD_TIMELINE=<file> (Horovod's own switch; the reference's launcher forwards such variables with -x,
+    run-tf-sing-ucx-openmpi.sh:104-106) produces a Chrome trace with one LAUNCH event per fusion bucket and step."""
+    import json
+    path = tmp_path / "timeline.json"
+    monkeypatch.setenv("HOROVOD_TIMELINE", str(path))
+    argv = ["--model=lenet", "--batch_size=4", "--num_batches=2", "--num_warmup_batches=1", "--device=cpu",
+            "--variable_update=horovod", "--display_every=1", "--fusion_threshold=65536"]
+    testing.run_ranks(W.w_cli, 2, "gloo", args=(argv,), timeout=600)
+    ev = json.load(open(path))
+    launches = [e for e in ev if e.get("cat") == "LAUNCH" or e.get("args", {}).get("phase") == "LAUNCH" or "bucket" in e.get("name", "")]
+    assert len(launches) >= 3 * 2, ev[:3]
+
+
+def test_lr_schedule_drives_the_flat_optimizer():
+    from azure_hc_intel_tf_b200 import hvd
+    net = torch.nn.Linear(8, 4)
+    opt = hvd.MomentumSGD(list(net.named_parameters()), lr=1.0, momentum=0.0)
+    opt.lr_schedule = lambda step: 0.5 if step == 0 else 0.25
+    w0 = net.weight.detach().clone()
+    net(torch.ones(2, 8)).sum().backward()
+    g = net.weight.grad.detach().clone()
+    opt.step()
+    assert torch.allclose(net.weight.detach(), w0 - 0.5 * g)
+    w1 = net.weight.detach().clone()
+    opt.step()                                      # same gradient (not zeroed), second rate
+    assert torch.allclose(net.weight.detach(), w1 - 0.25 * g) and opt.lr == 0.25
