@@ -219,10 +219,12 @@ class SymmetricContext:
         # upper bound on CTAs per collective (128 threads each); small messages use fewer (one per four blocks)
         self.ctas = int(os.environ.get("B200_COMM_CTAS", "96"))
         # messages up to this many bytes use the one-shot kernel (one NVLink traversal); 0 disables it
-        self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(128 << 10)))
+        # (thresholds from the per-algorithm sweeps in profiles/osu/: at 8 GPUs one-shot and two-shot tie up to 256 KiB
+        # and the in-switch reduction wins from 64 KiB on; at 2 GPUs everything up to 1 MiB is flat at the barrier cost)
+        self.one_shot_max_bytes = int(os.environ.get("B200_COMM_ONE_SHOT_MAX", str(32 << 10)))
         # messages of at least this many bytes use the NVLS (in-switch reduction) kernel when the buffer has a
         # multicast mapping; -1 disables NVLS. With two ranks a direct peer read is the shorter path.
-        default_nvls = (8 << 20) if world > 2 else -1
+        default_nvls = (64 << 10) if world > 2 else -1
         self.nvls_min_bytes = int(os.environ.get("B200_COMM_NVLS_MIN", str(default_nvls)))
         self.algo = ALGOS[os.environ.get("B200_COMM_ALGO", "auto")]
         self.nvls_ok = None      # decided collectively at the first multicast allocation
