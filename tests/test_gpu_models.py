@@ -24,7 +24,8 @@ def test_two_training_steps_on_the_kernel_path(name):
         loss = b.step()
     torch.cuda.synchronize()
     v = float(loss.detach())
-    assert v == v and 0.0 < v < 100.0, v
+    # (the 'trivial' model is one affine layer on raw pixels: its first losses are in the thousands)
+    assert v == v and 0.0 < v < (1e5 if name == "trivial" else 100.0), v
     assert b200.launch_count > 0
     paths = dict(conv_impl.path_counts)
     # layers whose channel counts are multiples of 8 never leave the tensor-core kernels
