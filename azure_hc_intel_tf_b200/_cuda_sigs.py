@@ -59,6 +59,11 @@ OPTIONAL = {
     "b200_conv_dgrad_strided_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_conv_wgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
     "b200_conv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
+    "b200_dwconv_supported": (i32, [C.POINTER(ConvGeom)]),
+    "b200_dwconv_fprop": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp]),
+    "b200_dwconv_dgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp]),
+    "b200_dwconv_wgrad": (i32, [vp, vp, vp, C.POINTER(ConvGeom), vp, vp]),
+    "b200_dwconv_wgrad_workspace_bytes": (i64, [C.POINTER(ConvGeom)]),
     "b200_gemm_nt": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "b200_gemm_nt_stats": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
     "b200_gemm_stats_rows": (i64, [i32, i32]),

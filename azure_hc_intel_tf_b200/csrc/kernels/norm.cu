@@ -315,6 +315,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restri
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float sc[8], sh[8];
+  const float hi = relu == 2 ? 6.0f : __int_as_float(0x7f800000);   // relu == 2: ReLU6 (the mask records 0 < f < 6)
   if (fixed && i < nvec) {
     const int ch = (int)(i % cvecs) * 8;
     load8f(scale + ch, sc);
@@ -351,11 +352,11 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const b200_bf16* __restri
         if (mask_out) {
           unsigned mb = 0;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) mb |= (f[k] > 0.0f ? 1u : 0u) << k;
+          for (int k = 0; k < 8; ++k) mb |= (f[k] > 0.0f && f[k] < hi ? 1u : 0u) << k;
           mask_out[idx] = (uint8_t)mb;
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.0f);
+        for (int k = 0; k < 8; ++k) f[k] = fminf(fmaxf(f[k], 0.0f), hi);
       }
       st8(z + idx * 8, pack8(f));
     }

@@ -40,6 +40,9 @@ class BuildConfig:
     num_classes: int = 1001         # tf_cnn_benchmarks ImageNet has a background class
 
 
+ACT_MODE = {None: 0, "linear": 0, "relu": 1, "relu6": 2}     # the ``relu`` argument of the ops layer
+
+
 def same_padding(size: int, k: int, s: int) -> Tuple[int, int]:
     """TensorFlow 'SAME' padding (lo, hi) for one spatial dim."""
     out = -(-size // s)
@@ -52,10 +55,12 @@ class Conv(nn.Module):
 
     def __init__(self, cfg: BuildConfig, cin: int, cout: int, k: IntPair, stride: IntPair, mode: str,
                  in_hw: Tuple[int, int], use_bn: bool, activation: Optional[str], bias: Optional[float],
-                 stddev: Optional[float], scope: str, bn_scope: str):
+                 stddev: Optional[float], scope: str, bn_scope: str, groups: int = 1):
         super().__init__()
         self.cfg = cfg
         self.cin, self.cout = cin, cout
+        self.groups = groups                      # cin == cout == groups: depthwise (MobileNet)
+        assert cin % groups == 0 and cout % groups == 0
         self.k, self.stride = _pair(k), _pair(stride)
         self.activation = activation
         self.scope = scope
@@ -74,16 +79,21 @@ class Conv(nn.Module):
             raise ValueError(mode)
         self.pad = (ph, pw)                       # ((top,bottom),(left,right))
         self.out_hw = ((in_hw[0] + ph[0] + ph[1] - kh) // sh + 1, (in_hw[1] + pw[0] + pw[1] - kw) // sw + 1)
-        w = torch.empty(cout, cin, kh, kw)
+        w = torch.empty(cout, cin // groups, kh, kw)
         if stddev is not None:
             nn.init.trunc_normal_(w, std=stddev, a=-2 * stddev, b=2 * stddev)
         else:
             # variance_scaling_initializer() default: fan_in, factor 2, truncated normal
-            std = math.sqrt(2.0 / (cin * kh * kw))
+            std = math.sqrt(2.0 / (cin // groups * kh * kw))
             nn.init.trunc_normal_(w, std=std, a=-2 * std, b=2 * std)
         self.weight = nn.Parameter(w.contiguous(memory_format=torch.channels_last))
-        self.weight.tf_name = f"{scope}/conv2d/kernel"
-        self.weight.tf_layout = "HWIO"
+        if groups > 1:
+            # tf.nn.depthwise_conv2d keeps its filter as [kh, kw, in_channels, channel_multiplier]
+            self.weight.tf_name = f"{scope}/depthwise_conv2d/depthwise_kernel"
+            self.weight.tf_layout = "HWC1"
+        else:
+            self.weight.tf_name = f"{scope}/conv2d/kernel"
+            self.weight.tf_layout = "HWIO"
         self.weight.decay = True
         if use_bn:
             self.bias = None
@@ -98,12 +108,12 @@ class Conv(nn.Module):
             else:
                 self.bias = None
 
-    def forward(self, x):
-        relu = self.activation == "relu"
-        return ops.conv_block(x, self, relu=relu)
+    def forward(self, x, residual=None):
+        return ops.conv_block(x, self, relu=ACT_MODE[self.activation], residual=residual)
 
     def extra_repr(self):
-        return f"{self.cin}->{self.cout} k={self.k} s={self.stride} pad={self.pad} act={self.activation} [{self.scope}]"
+        g = f" groups={self.groups}" if self.groups > 1 else ""
+        return f"{self.cin}->{self.cout} k={self.k} s={self.stride} pad={self.pad}{g} act={self.activation} [{self.scope}]"
 
 
 class BatchNorm(nn.Module):
@@ -139,7 +149,7 @@ class BNAct(nn.Module):
         self.activation = activation
 
     def forward(self, x):
-        return ops.batch_norm(x, self.bn, relu=self.activation == "relu")
+        return ops.batch_norm(x, self.bn, relu=ACT_MODE[self.activation])
 
 
 class Affine(nn.Module):
@@ -251,7 +261,8 @@ class ConvNetBuilder:
     # -- layers
     def conv(self, cout: int, k: IntPair, stride: IntPair = 1, mode: str = "SAME", cin: Optional[int] = None,
              in_hw=None, use_batch_norm: Optional[bool] = None, activation: Optional[str] = "relu",
-             bias: Optional[float] = 0.0, stddev: Optional[float] = None, advance: bool = True) -> Conv:
+             bias: Optional[float] = 0.0, stddev: Optional[float] = None, advance: bool = True,
+             groups: int = 1) -> Conv:
         cin = self.c if cin is None else cin
         in_hw = self.hw if in_hw is None else in_hw
         use_bn = self.use_batch_norm if use_batch_norm is None else use_batch_norm
@@ -259,7 +270,7 @@ class ConvNetBuilder:
         bn_scope = f"batchnorm{self.counts['batchnorm']}"
         if use_bn:
             self.counts["batchnorm"] += 1
-        m = Conv(self.cfg, cin, cout, k, stride, mode, in_hw, use_bn, activation, bias, stddev, scope, bn_scope)
+        m = Conv(self.cfg, cin, cout, k, stride, mode, in_hw, use_bn, activation, bias, stddev, scope, bn_scope, groups)
         if advance:
             self.c, self.hw = cout, m.out_hw
         return m

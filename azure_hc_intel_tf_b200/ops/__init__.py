@@ -34,35 +34,41 @@ def _sym(pad):
 
 # ------------------------------------------------------------------------------------ conv block
 
-def conv_block(x, m, relu: bool):
-    """conv (+bias) (+training-mode batch-norm) (+ReLU)."""
+def _act(y, relu):
+    """``relu``: 0 / False = none, 1 / True = ReLU, 2 = ReLU6 (MobileNet)."""
+    if int(relu) == 2:
+        return F.relu6(y, inplace=True)
+    return F.relu(y, inplace=True) if relu else y
+
+
+def conv_block(x, m, relu, residual=None):
+    """conv (+bias) (+training-mode batch-norm (+residual)) (+ReLU | ReLU6); grouped when ``m.groups`` > 1."""
     if m.cfg.kernels == "b200" and _vec8(m.cout) and (_vec8(m.cin) or m.cin < 8):
-        return _b200().conv_block(x, m, relu)
+        return _b200().conv_block(x, m, relu, residual=residual)
     (pt, pb), (pl, pr) = m.pad
     w = m.weight if m.weight.dtype == x.dtype else m.weight.to(x.dtype)
     bias = None if (m.bn is not None or m.bias is None) else m.bias.to(x.dtype)
+    groups = getattr(m, "groups", 1)
     if _sym(m.pad):
-        y = F.conv2d(x, w, bias, m.stride, (pt, pl))
+        y = F.conv2d(x, w, bias, m.stride, (pt, pl), 1, groups)
     else:
-        y = F.conv2d(F.pad(x, (pl, pr, pt, pb)), w, bias, m.stride)
+        y = F.conv2d(F.pad(x, (pl, pr, pt, pb)), w, bias, m.stride, 0, 1, groups)
     if m.bn is not None:
-        y = batch_norm(y, m.bn, relu=relu)
-    elif relu:
-        y = F.relu(y, inplace=True)
-    return y
+        return batch_norm(y, m.bn, relu=relu, residual=residual)
+    if residual is not None:
+        y = y + residual
+    return _act(y, relu)
 
 
-def batch_norm(y, bn, relu: bool = False, residual=None):
-    """Training-mode BN; optional fused residual add and ReLU (y = relu(bn(y) + residual))."""
+def batch_norm(y, bn, relu=False, residual=None):
+    """Training-mode BN; optional fused residual add and ReLU / ReLU6 (y = act(bn(y) + residual))."""
     if bn.cfg.kernels == "b200" and _vec8(y.shape[1]) and y.dim() == 4:
         return _b200().batch_norm(y, bn, relu, residual)
     out = F.batch_norm(y, bn.moving_mean, bn.moving_variance, bn.gamma, bn.beta, bn.training,
                        1.0 - bn.decay, bn.eps)
     if residual is not None:
         out = out + residual
-    if relu:
-        out = F.relu(out, inplace=True)
-    return out
+    return _act(out, relu)
 
 
 def conv_bn_add_relu(x, m, residual):

@@ -120,8 +120,10 @@ def bn_forward(y, bn, residual, relu, sums=None, want_mask=False):
         scale.copy_(bn.gamma.detach() * rstd)
         shift.copy_(bn.beta.detach() - mean * scale)
     z = empty_nhwc(n, c, h, w, dev)
-    # with a residual the ReLU mask cannot be recomputed from y: keep it as one bit per element for the backward
-    mask = torch.empty(rows * c // 8, dtype=torch.uint8, device=dev) if (relu and residual is not None and want_mask) else None
+    # with a residual the ReLU mask cannot be recomputed from y: keep it as one bit per element for the backward;
+    # ReLU6 (relu == 2) always keeps it - its pass-through set is 0 < f < 6, which the backward kernels take from the mask
+    keep = relu and want_mask and (residual is not None or int(relu) == 2)
+    mask = torch.empty(rows * c // 8, dtype=torch.uint8, device=dev) if keep else None
     _check(lib().b200_bn_apply(_ptr(y), _ptr(residual), _ptr(z), _ptr(mask), rows, c, _ptr(scale), _ptr(shift), int(relu),
                                _stream()), "bn_apply")
     return (z, stats, mask) if want_mask else (z, stats)
@@ -167,6 +169,7 @@ def _cb_forward(x, weight, m, relu, residual):
     if not first:
         y = conv_impl.fprop(x, w_lp, m)
     if m.bias is not None or relu:
+        assert int(relu) != 2, "ReLU6 is only implemented behind batch-norm (MobileNet)"
         n, c, h, w = y.shape
         _check(lib().b200_bias_act(_ptr(y), _ptr(m.bias), _ptr(y), n * h * w, c, int(relu), _stream()), "bias_act")
     return y, (x, w_lp, None, y if relu else None, None, first)

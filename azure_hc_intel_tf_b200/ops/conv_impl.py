@@ -37,6 +37,10 @@ def _sym(m):
     return pt == pb and pl == pr
 
 
+def _groups(m) -> int:
+    return getattr(m, "groups", 1)
+
+
 def _padded(x, m):
     (pt, pb), (pl, pr) = m.pad
     return torch.nn.functional.pad(x, (pl, pr, pt, pb))
@@ -49,6 +53,16 @@ def fprop(x, w_lp, m, want_stats: bool = False):
     With ``want_stats`` returns ``(y, partials)`` where partials is [rows, 2, K] fp32 (per-CTA Σy, Σy² per
     channel, produced by the conv epilogue) or None when the path taken cannot produce them."""
     md = mode()
+    if _groups(m) > 1:
+        if md != "cudnn" and _umma().supports_depthwise(x.shape, m):
+            path_counts["fprop_depthwise"] += 1
+            y = _umma().dw_fprop(x, w_lp, m)
+        else:
+            if md == "umma":
+                raise RuntimeError(f"B200_CONV=umma but the depthwise kernels do not cover {m.extra_repr()}")
+            path_counts["fprop_lib"] += 1
+            y = _fprop_lib(x, w_lp, m)
+        return (y, None) if want_stats else y
     if md != "cudnn":
         u = _umma()
         if u.supports_fprop(x, w_lp, m):
@@ -65,15 +79,18 @@ def fprop(x, w_lp, m, want_stats: bool = False):
 
 def _fprop_lib(x, w_lp, m):
     if _sym(m):
-        y = torch.ops.aten.convolution(x, w_lp, None, m.stride, (m.pad[0][0], m.pad[1][0]), (1, 1), False, (0, 0), 1)
+        y = torch.ops.aten.convolution(x, w_lp, None, m.stride, (m.pad[0][0], m.pad[1][0]), (1, 1), False, (0, 0), _groups(m))
     else:
-        y = torch.ops.aten.convolution(_padded(x, m), w_lp, None, m.stride, (0, 0), (1, 1), False, (0, 0), 1)
+        y = torch.ops.aten.convolution(_padded(x, m), w_lp, None, m.stride, (0, 0), (1, 1), False, (0, 0), _groups(m))
     return y if y.is_contiguous(memory_format=torch.channels_last) else y.contiguous(memory_format=torch.channels_last)
 
 
 def dgrad(dy, w_lp, m, x_shape):
     md = mode()
-    if md != "cudnn":
+    if _groups(m) > 1 and md != "cudnn" and _umma().supports_depthwise(x_shape, m):
+        path_counts["dgrad_depthwise"] += 1
+        return _umma().dw_dgrad(dy, w_lp, m, x_shape)
+    if md != "cudnn" and _groups(m) == 1:
         u = _umma()
         if u.supports_dgrad(dy, w_lp, m, x_shape):
             path_counts["dgrad_umma"] += 1
@@ -88,7 +105,7 @@ def dgrad(dy, w_lp, m, x_shape):
     else:
         xs, pad = (n, c, h + pt + pb, w + pl + pr), (0, 0)
     fake_x = dy.new_empty(xs).contiguous(memory_format=torch.channels_last)   # only its shape is used
-    dx, _, _ = torch.ops.aten.convolution_backward(dy, fake_x, w_lp, None, m.stride, pad, (1, 1), False, (0, 0), 1,
+    dx, _, _ = torch.ops.aten.convolution_backward(dy, fake_x, w_lp, None, m.stride, pad, (1, 1), False, (0, 0), _groups(m),
                                                    [True, False, False])
     if not _sym(m):
         dx = dx[:, :, pt:pt + h, pl:pl + w]
@@ -98,7 +115,10 @@ def dgrad(dy, w_lp, m, x_shape):
 def wgrad(x, dy, m, out=None):
     """Returns fp32 [K,C,R,S] (channels_last); when ``out`` (fp32 view, same layout) is given it is filled."""
     md = mode()
-    if md != "cudnn":
+    if _groups(m) > 1 and md != "cudnn" and _umma().supports_depthwise(x.shape, m):
+        path_counts["wgrad_depthwise"] += 1
+        return _umma().dw_wgrad(x, dy, m, out)
+    if md != "cudnn" and _groups(m) == 1:
         u = _umma()
         if u.supports_wgrad(x, dy, m):
             path_counts["wgrad_umma"] += 1
@@ -106,11 +126,11 @@ def wgrad(x, dy, m, out=None):
         if md == "umma":
             raise RuntimeError(f"B200_CONV=umma but wgrad does not cover {m.extra_repr()}")
     path_counts["wgrad_lib"] += 1
-    k, c = m.cout, m.cin
+    k, c = m.cout, m.cin // _groups(m)
     r, s = m.k
     xx, pad = (x, (m.pad[0][0], m.pad[1][0])) if _sym(m) else (_padded(x, m), (0, 0))
     fake_w = x.new_empty((k, c, r, s)).contiguous(memory_format=torch.channels_last)
-    _, dw, _ = torch.ops.aten.convolution_backward(dy, xx, fake_w, None, m.stride, pad, (1, 1), False, (0, 0), 1,
+    _, dw, _ = torch.ops.aten.convolution_backward(dy, xx, fake_w, None, m.stride, pad, (1, 1), False, (0, 0), _groups(m),
                                                    [False, True, False])
     if out is not None:
         out.copy_(dw)

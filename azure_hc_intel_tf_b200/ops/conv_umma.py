@@ -108,6 +108,39 @@ def wgrad(x, dy, m, out=None):
     return out
 
 
+# ------------------------------------------------------------------------------------ depthwise (csrc/kernels/depthwise.cu)
+
+def supports_depthwise(x_shape, m) -> bool:
+    if "depthwise" in _disabled or m.groups != m.cin or m.cin != m.cout:
+        return False
+    fn = getattr(lib(), "b200_dwconv_supported", None)
+    return bool(fn and fn(C.byref(geom(x_shape, m))))
+
+
+def dw_fprop(x, w_lp, m):
+    g = geom(x.shape, m)
+    y = empty_nhwc(g.n, g.k, g.p, g.q, x.device)
+    _check(lib().b200_dwconv_fprop(_ptr(x), _ptr(w_lp), _ptr(y), C.byref(g), _stream()), "dwconv_fprop")
+    return y
+
+
+def dw_dgrad(dy, w_lp, m, x_shape):
+    g = geom(x_shape, m)
+    dx = empty_nhwc(g.n, g.c, g.h, g.w, dy.device)
+    _check(lib().b200_dwconv_dgrad(_ptr(dy), _ptr(w_lp), _ptr(dx), C.byref(g), _stream()), "dwconv_dgrad")
+    return dx
+
+
+def dw_wgrad(x, dy, m, out=None):
+    g = geom(x.shape, m)
+    if out is None:
+        out = torch.empty((g.k, g.r, g.s, 1), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+    ws = _workspace(lib().b200_dwconv_wgrad_workspace_bytes(C.byref(g)), x.device)
+    _check(lib().b200_dwconv_wgrad(_ptr(x), _ptr(dy), _ptr(out), C.byref(g), _ptr(ws), _stream()), "dwconv_wgrad")
+    b200.count_launch(1)
+    return out
+
+
 def gemm_nt(a, b, out_fp32: bool = False):
     mm, kk = a.shape
     nn = b.shape[0]

@@ -25,6 +25,8 @@ GLOBAL_STEP = "global_step"
 def to_tf_layout(t: torch.Tensor, layout: str) -> torch.Tensor:
     if layout == "HWIO":
         return t.permute(2, 3, 1, 0).contiguous()
+    if layout == "HWC1":                       # depthwise [C,1,R,S] -> [R,S,C,1]
+        return t.permute(2, 3, 0, 1).contiguous()
     if layout == "IO":
         return t.t().contiguous()
     return t.contiguous()
@@ -33,6 +35,8 @@ def to_tf_layout(t: torch.Tensor, layout: str) -> torch.Tensor:
 def from_tf_layout(t: torch.Tensor, layout: str) -> torch.Tensor:
     if layout == "HWIO":
         return t.permute(3, 2, 0, 1)
+    if layout == "HWC1":
+        return t.permute(2, 3, 0, 1)
     if layout == "IO":
         return t.t()
     return t

@@ -99,7 +99,9 @@ int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows
                               const float* beta, float* running_mean, float* running_var, float decay, float eps,
                               float* mean, float* rstd, float* scale, float* shift, void* stream);
 
-/* z = act(scale*x + shift (+ residual)); relu != 0 applies max(0, .). residual may be NULL. In place allowed.
+/* z = act(scale*x + shift (+ residual)); relu == 1 applies max(0, .), relu == 2 ReLU6 = min(max(0, .), 6) (MobileNet;
+ * pass relu_mask then: the backward kernels take the pass-through set 0 < f < 6 from it). residual may be NULL. In
+ * place allowed.
  * relu_mask (optional, rows*c/8 bytes): bit k of byte v = (element 8v+k passed the ReLU); the backward kernels read
  * it instead of z, 16x fewer bytes — used when the mask cannot be recomputed from x alone (residual add). */
 int b200_bn_apply(const b200_bf16* x, const b200_bf16* residual, b200_bf16* z, uint8_t* relu_mask, int64_t rows,

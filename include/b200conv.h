@@ -64,6 +64,16 @@ int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b2
                     void* stream);
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
 
+/* Depthwise convolution (groups == channels; g->k == g->c, c % 8 == 0, at most 9 filter taps; filters [C][R][S] = the
+ * KRSC layout of a [C,1,R,S] weight, filter gradient fp32 in the same layout). Bandwidth-bound vector kernels
+ * (csrc/kernels/depthwise.cu): MobileNet's 3x3 depthwise layers. wgrad folds its per-CTA partials in a fixed order. */
+int b200_dwconv_supported(const b200_conv_geom* g);
+int b200_dwconv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, void* stream);
+int b200_dwconv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);
+int b200_dwconv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
+                      void* stream);
+int64_t b200_dwconv_wgrad_workspace_bytes(const b200_conv_geom* g);
+
 /* out[m, n] = a[m, k] . b[n, k]^T ; a, b row-major bf16, k % 64 == 0; out bf16 or fp32 with leading dimension ldo. */
 int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
                  int32_t out_fp32, void* stream);

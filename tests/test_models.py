@@ -12,7 +12,7 @@ from azure_hc_intel_tf_b200.models import available_models, create_model
 EXPECTED_PARAMS = {          # trainable parameters with 1001 classes
     "resnet50": 25559081, "resnet101": 44551209, "resnet152": 60194857, "vgg16": 138361641, "vgg19": 143671337,
     "inception3": 23819401, "googlenet": 6999577, "alexnet": 61842345,
-    "resnet50_v2": 25551529, "inception4": 42649769,
+    "resnet50_v2": 25551529, "inception4": 42649769, "mobilenet": 3506153,
     # CIFAR-10 models (11 classes): the published sizes are 0.27 M / 0.85 M / 1.7 M (ResNet-20/56/110) and
     # 1.0 M / 7.0 M / 27.2 M (DenseNet 40-k12 / 100-k12 / 100-k24)
     "resnet20": 269787, "resnet56": 853083, "resnet110": 1728027, "resnet20_v2": 269787,
@@ -34,7 +34,7 @@ def test_resnet50_has_161_trainable_tensors_and_53_convs():
 
 
 @pytest.mark.parametrize("name", ["resnet50", "googlenet", "lenet", "trivial", "resnet50_v2", "resnet20", "resnet32_v2",
-                                  "densenet40_k12", "inception4"])
+                                  "densenet40_k12", "inception4", "mobilenet"])
 def test_forward_backward_shapes(name):
     m = create_model(name)
     x = torch.randn(2, 3, m.image_size, m.image_size).contiguous(memory_format=torch.channels_last)
@@ -73,3 +73,40 @@ def test_bench_reference_arm_reports_unavailable():
     out = subprocess.run([sys.executable, "bench.py", "--impl", "reference"], capture_output=True, text=True, check=True)
     d = json.loads(out.stdout.strip().splitlines()[-1])
     assert d["impl"] == "reference" and "unavailable" in d
+
+
+def test_mobilenet_depthwise_layers_and_checkpoint_layout(tmp_path):
+    """17 depthwise 3x3 layers with ReLU6; their filters go to a checkpoint in TF's [kh, kw, C, 1] layout and back."""
+    from azure_hc_intel_tf_b200.models.builder import Conv
+    from azure_hc_intel_tf_b200.utils import tfnames
+    m = create_model("mobilenet_v2")
+    dw = [c for c in m.modules() if isinstance(c, Conv) and c.groups > 1]
+    assert len(dw) == 17 and all(c.groups == c.cin == c.cout and c.k == (3, 3) and c.activation == "relu6" for c in dw)
+    assert sum(1 for c in m.modules() if isinstance(c, Conv)) == 52
+    w = dw[3].weight.detach()
+    assert dw[3].weight.tf_layout == "HWC1" and dw[3].weight.tf_name.endswith("depthwise_conv2d/depthwise_kernel")
+    t = tfnames.to_tf_layout(w, "HWC1")
+    assert t.shape == (3, 3, w.shape[0], 1)
+    assert torch.equal(tfnames.from_tf_layout(t, "HWC1"), w)
+    # linear bottleneck: the projection has no activation and takes the block input as the fused residual
+    blk = m.blocks[2]
+    assert blk.use_res and blk.project.activation is None and not m.blocks[1].use_res
+
+
+def test_relu6_and_grouped_conv_on_the_stock_path_match_torch():
+    import torch.nn.functional as F
+    from azure_hc_intel_tf_b200.models.builder import BuildConfig, ConvNetBuilder
+    torch.manual_seed(0)
+    cfg = BuildConfig(kernels="cudnn", use_batch_norm=True, bn_scale=True)
+    b = ConvNetBuilder(cfg, 16, (9, 9))
+    c = b.conv(16, 3, 2, "SAME", activation="relu6", groups=16, bias=None)
+    x = torch.randn(2, 16, 9, 9) * 4
+    y = c(x)
+    (pt, pb), (pl, pr) = c.pad
+    ref = F.conv2d(F.pad(x, (pl, pr, pt, pb)), c.weight, None, 2, 0, 1, 16)
+    ref = F.relu6(F.batch_norm(ref, None, None, c.bn.gamma, c.bn.beta, True, 0.0, c.bn.eps))
+    assert y.shape == (2, 16, 5, 5) and torch.allclose(y, ref, atol=1e-5)
+    r = torch.randn_like(ref)
+    c.activation = None
+    assert torch.allclose(c(x, residual=r), F.batch_norm(F.conv2d(F.pad(x, (pl, pr, pt, pb)), c.weight, None, 2, 0, 1, 16),
+                                                         None, None, c.bn.gamma, c.bn.beta, True, 0.0, c.bn.eps) + r, atol=1e-5)
