@@ -279,7 +279,7 @@ __device__ __forceinline__ void next_run(RunIter& it, const RunStep& st, int chu
 }
 
 template <int ST, int V>
-__global__ void __launch_bounds__(256, V == 4 ? 2 : 1)
+__global__ void __launch_bounds__(256, V == 4 ? 3 : 1)
 dw3_fwd_kernel(const b200_bf16* __restrict__ x, const b200_bf16* __restrict__ w, b200_bf16* __restrict__ y, DwGeom g,
                int chunks, RunStep step) {
   constexpr int NC = (kT - 1) * ST + 3;
@@ -338,7 +338,7 @@ __device__ __forceinline__ void dgrad_row(float acc[kT][V], const Vec<V>* L, con
 // dx: a thread produces the kT pixels w0, w0 + ST, ... of one stride phase of a row, so that all of them use the same
 // filter columns (s == (w + pl) mod ST) and consecutive dy columns. chunks = ST * cpp, phase-major.
 template <int ST, int V>
-__global__ void __launch_bounds__(256, V == 4 ? 2 : 1)
+__global__ void __launch_bounds__(256, V == 4 ? 3 : 2)
 dw3_dgrad_kernel(const b200_bf16* __restrict__ dy, const b200_bf16* __restrict__ w, b200_bf16* __restrict__ dx, DwGeom g,
                  int cpp, RunStep step) {
   constexpr int MM = 2 / ST, NL = kT + MM;

@@ -14,7 +14,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "azure_hc_intel_tf_b200", "_lib", "libb200cnn.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEYS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "LDGMC", "SYNCS", "UCGABAR", "HMMA", "MEMBAR"]
+KEYS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "LDGMC", "SYNCS", "UCGABAR", "FHFMA", "HMMA", "MEMBAR"]
 
 
 def demangle(names):
@@ -80,7 +80,8 @@ def main():
                 "LDTM = tcgen05.ld, UTMALDG / UTMASTG = TMA load / store (`.IM2COL`, `.2CTA` variants included), "
                 "LDGMC = multimem.ld_reduce (NVSwitch in-switch reduction; multimem.st assembles to a STG on the "
                 "multicast address), `.SYS` = loads / stores / reductions at system scope (peer memory, flags), "
-                "UCGABAR = cluster barrier, HMMA = legacy mma.sync (none anywhere).\n\n")
+                "UCGABAR = cluster barrier, FHFMA = mixed-precision bf16 x bf16 + fp32 FMA (the depthwise kernels), HMMA = legacy "
+                "mma.sync (none anywhere).\n\n")
         f.write("| kernel | file | instr | " + " | ".join(KEYS) + " | .SYS ld/st |\n|---|---|---:|" + "---:|" * (len(KEYS) + 1) + "\n")
         for name, fn, n, ops, sysn in rows:
             f.write(f"| `{name[:80]}` | [{fn[:40]}…]({fn}) | {n} | " + " | ".join(str(ops.get(k, 0) or "") for k in KEYS) + f" | {sysn or ''} |\n")
