@@ -19,6 +19,8 @@ SIGS = {
     "b200_version": (C.c_char_p, []),
     "b200_last_error": (C.c_char_p, []),
     "b200_sgd_momentum_flat": (i32, [vp, vp, vp, vp, i64, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp]),
+    "b200_rmsprop_flat": (i32, [vp, vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, f32, f32, f32, vp, vp]),
+    "b200_adam_flat": (i32, [vp, vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, f32, f32, f32, vp, vp]),
     "b200_lars_norms": (i32, [vp, vp, i64, vp, vp, f32, vp]),
     "b200_lars_trust_det": (i32, [vp, vp, i64, vp, vp, vp, vp, vp, vp, i32, f32, f32, f32, f32, vp]),
     "b200_lars_trust": (i32, [vp, vp, vp, vp, i32, f32, f32, f32, vp]),

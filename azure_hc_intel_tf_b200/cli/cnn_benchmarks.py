@@ -92,11 +92,13 @@ class BenchmarkCNN:
         p = self.p
         named = [(n, q) for n, q in self.model.named_parameters() if q.requires_grad]
         thr = flags_mod.resolve_fusion_threshold(p, self.fabric if self.world > 1 else None)
-        native = p.optimizer in ("momentum", "sgd", "lars") and not (self.kernels == "cudnn" and self.fabric == "nccl")
+        native = not (self.kernels == "cudnn" and self.fabric == "nccl")
         if native:
-            mu = 0.0 if p.optimizer == "sgd" else p.momentum
+            # every --optimizer runs on the plan-ordered flat buffers with its own update kernel (csrc/kernels/optim.cu)
+            mu = 0.0 if p.optimizer in ("sgd", "adam") else p.momentum
+            rule = p.optimizer if p.optimizer in ("rmsprop", "adam") else "momentum"
             opt = hvd.MomentumSGD(named, lr=self.lr, momentum=mu, weight_decay=p.weight_decay,
-                                  lars=p.optimizer == "lars", lars_eta=p.lars_eta,
+                                  lars=p.optimizer == "lars", lars_eta=p.lars_eta, rule=rule,
                                   lowp=self.kernels == "b200", fusion_threshold=thr,
                                   fusion_tail=flags_mod.resolve_fusion_tail(self.fabric if self.world > 1 else None))
             if p.lr_schedule != "constant" or p.num_learning_rate_warmup_epochs > 0:
@@ -104,7 +106,7 @@ class BenchmarkCNN:
                 opt.lr_schedule = lr_schedule.make(p.lr_schedule, self.lr, self.global_batch,
                                                    p.num_learning_rate_warmup_epochs, p.num_epochs_total, n_img)
         else:
-            # stock-library baseline (and rmsprop / adam): torch.optim on the fp32 parameters
+            # stock-library baseline arm: torch.optim on the fp32 parameters
             ps = [q for _, q in named]
             if p.optimizer in ("momentum", "sgd", "lars"):
                 opt = torch.optim.SGD(ps, lr=self.lr, momentum=0.0 if p.optimizer == "sgd" else p.momentum,

@@ -48,6 +48,59 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ w, fl
   }
 }
 
+// RMSProp and Adam on the same flat buffers (TensorFlow semantics, as tf_cnn_benchmarks --optimizer=rmsprop|adam builds
+// them): kRule 1: ms = rho*ms + (1-rho)*g^2; mom = mu*mom + lr*g/sqrt(ms + eps); w -= mom   (ApplyRMSProp)
+//       kRule 2: m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2; w -= lr_t*m/(sqrt(v) + eps)     (ApplyAdam; lr_t carries
+//                the bias correction lr*sqrt(1-b2^t)/(1-b1^t), computed on the host and read from lr_dev)
+// s1 is the first-moment-like slot (mom / m), s2 the second-moment slot (ms / v). g includes 1/N and weight decay.
+template <int kRule>
+__global__ void __launch_bounds__(256) adaptive_flat_kernel(float* __restrict__ w, float* __restrict__ s1, float* __restrict__ s2,
+                                                            const float* __restrict__ g, b200_bf16* __restrict__ shadow,
+                                                            int64_t nblk, const int32_t* __restrict__ block_tensor,
+                                                            const float* __restrict__ tdecay, float lr, float a, float b,
+                                                            float eps, float wd, float gscale,
+                                                            const float* __restrict__ lr_dev) {
+  if (lr_dev) lr = __ldg(lr_dev);
+  for (int64_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+    float dec = wd;
+    if (block_tensor) {
+      int t = block_tensor[blk];
+      if (t < 0) continue;
+      dec = wd * tdecay[t];
+    }
+    int64_t i = blk * 1024 + threadIdx.x * 4;
+    float4 wv = *reinterpret_cast<const float4*>(w + i);
+    float4 av = *reinterpret_cast<const float4*>(s1 + i);
+    float4 bv = *reinterpret_cast<const float4*>(s2 + i);
+    float4 gv = __ldcs(reinterpret_cast<const float4*>(g + i));
+    float ww[4] = {wv.x, wv.y, wv.z, wv.w}, aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
+    float gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float ge = gg[k] * gscale + dec * ww[k];
+      if (kRule == 1) {
+        bb[k] = a * bb[k] + (1.0f - a) * ge * ge;
+        aa[k] = b * aa[k] + lr * ge * rsqrtf(bb[k] + eps);
+        ww[k] -= aa[k];
+      } else {
+        aa[k] = a * aa[k] + (1.0f - a) * ge;
+        bb[k] = b * bb[k] + (1.0f - b) * ge * ge;
+        ww[k] -= lr * aa[k] / (sqrtf(bb[k]) + eps);
+      }
+    }
+    *reinterpret_cast<float4*>(w + i) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+    *reinterpret_cast<float4*>(s1 + i) = make_float4(aa[0], aa[1], aa[2], aa[3]);
+    *reinterpret_cast<float4*>(s2 + i) = make_float4(bb[0], bb[1], bb[2], bb[3]);
+    if (shadow) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(ww[0], ww[1]), hi = __floats2bfloat162_rn(ww[2], ww[3]);
+      uint2 pk;
+      pk.x = *reinterpret_cast<uint32_t*>(&lo);
+      pk.y = *reinterpret_cast<uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(shadow + i) = pk;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) lars_norms_kernel(const float* __restrict__ w, const float* __restrict__ g,
                                                          int64_t nblk, const int32_t* __restrict__ block_tensor,
                                                          float* __restrict__ norms, float gscale) {
@@ -181,6 +234,39 @@ int b200_sgd_momentum_flat(float* master, float* mom, const float* grad, b200_bf
                                                                       grad_scale, lr_dev);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+static int adaptive_flat(int rule, float* master, float* s1, float* s2, const float* grad, b200_bf16* shadow, int64_t n,
+                         const int32_t* block_tensor, const float* tensor_decay, float lr, float a, float b, float eps,
+                         float wd, float grad_scale, const float* lr_dev, void* stream) {
+  B200_CHECK_ARG(master && s1 && s2 && grad, "adaptive_flat: null pointer");
+  B200_CHECK_ARG(n > 0 && n % 1024 == 0, "adaptive_flat: n must be a positive multiple of 1024");
+  B200_CHECK_ARG(!block_tensor || tensor_decay, "adaptive_flat: block table needs tensor_decay");
+  int64_t nblk = n / 1024;
+  int grid = (int)(nblk < (int64_t)kNumSMs * 8 ? nblk : (int64_t)kNumSMs * 8);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (rule == 1)
+    adaptive_flat_kernel<1><<<grid, 256, 0, st>>>(master, s1, s2, grad, shadow, nblk, block_tensor, tensor_decay, lr, a, b,
+                                                  eps, wd, grad_scale, lr_dev);
+  else
+    adaptive_flat_kernel<2><<<grid, 256, 0, st>>>(master, s1, s2, grad, shadow, nblk, block_tensor, tensor_decay, lr, a, b,
+                                                  eps, wd, grad_scale, lr_dev);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_rmsprop_flat(float* master, float* mom, float* ms, const float* grad, b200_bf16* shadow, int64_t n,
+                      const int32_t* block_tensor, const float* tensor_decay, float lr, float rho, float mu, float eps,
+                      float wd, float grad_scale, const float* lr_dev, void* stream) {
+  return adaptive_flat(1, master, mom, ms, grad, shadow, n, block_tensor, tensor_decay, lr, rho, mu, eps, wd, grad_scale,
+                       lr_dev, stream);
+}
+
+int b200_adam_flat(float* master, float* m, float* v, const float* grad, b200_bf16* shadow, int64_t n,
+                   const int32_t* block_tensor, const float* tensor_decay, float lr_t, float beta1, float beta2, float eps,
+                   float wd, float grad_scale, const float* lr_dev, void* stream) {
+  return adaptive_flat(2, master, m, v, grad, shadow, n, block_tensor, tensor_decay, lr_t, beta1, beta2, eps, wd, grad_scale,
+                       lr_dev, stream);
 }
 
 int b200_lars_norms(const float* master, const float* grad, int64_t n, const int32_t* block_tensor, float* norms,

@@ -325,4 +325,4 @@ def broadcast_object(obj, root_rank: int = 0):
     return objs[0]
 
 
-from .optimizer import DistributedOptimizer, MomentumSGD, LARS  # noqa: E402,F401
+from .optimizer import DistributedOptimizer, MomentumSGD, LARS, RMSProp, Adam  # noqa: E402,F401

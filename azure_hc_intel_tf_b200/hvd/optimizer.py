@@ -53,7 +53,18 @@ class MomentumSGD:
 
     def __init__(self, params: Iterable, lr: float, momentum: float = 0.9, weight_decay: float = 0.0,
                  lars: bool = False, lars_eta: float = 0.001, lars_eps: float = 1e-9, lowp: bool = False,
-                 fusion_threshold: int = DEFAULT_THRESHOLD, grad_alloc=None, fusion_tail: int = 0):
+                 fusion_threshold: int = DEFAULT_THRESHOLD, grad_alloc=None, fusion_tail: int = 0,
+                 rule: str = "momentum", hyper: Optional[dict] = None):
+        if rule not in ("momentum", "rmsprop", "adam"):
+            raise ValueError(f"unknown update rule {rule!r}")
+        if rule != "momentum" and lars:
+            raise ValueError("LARS is a momentum-SGD variant")
+        # the update rule applied to the flat buffers: TF ApplyMomentum, ApplyRMSProp (rho, eps; ms starts at 1) or
+        # ApplyAdam (beta1, beta2, eps) - tf_cnn_benchmarks' --optimizer=momentum|sgd|rmsprop|adam with its defaults
+        self.rule = rule
+        self.hyper = {"momentum": {}, "rmsprop": {"rho": 0.9, "eps": 1.0},
+                      "adam": {"beta1": 0.9, "beta2": 0.999, "eps": 1e-8}}[rule]
+        self.hyper.update(hyper or {})
         named = []
         for i, p in enumerate(params):
             if isinstance(p, tuple):
@@ -83,7 +94,12 @@ class MomentumSGD:
         total = self.plan.total_elems[0]
         self.total = total
         self.master = torch.zeros(total, dtype=torch.float32, device=dev)
-        self.mom = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.mom = torch.zeros(total, dtype=torch.float32, device=dev)       # Momentum | RMSProp momentum | Adam m
+        self.state2 = None                                                    # RMSProp mean square | Adam v
+        if rule == "rmsprop":
+            self.state2 = torch.ones(total, dtype=torch.float32, device=dev)
+        elif rule == "adam":
+            self.state2 = torch.zeros(total, dtype=torch.float32, device=dev)
         self.grad = grad_alloc(total) if grad_alloc is not None else torch.zeros(total, dtype=torch.float32, device=dev)
         self.shadow = torch.zeros(total, dtype=torch.bfloat16, device=dev) if lowp else None
         self.ranges = []
@@ -110,30 +126,45 @@ class MomentumSGD:
         # the learning rate also lives in device memory: the update kernels read it from there, so a schedule (warm-up,
         # decay) keeps working when the whole step is replayed from a CUDA graph
         self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        self._lr_dev_value = float(lr)
         self.lr_schedule = None
         self._lars_tab = None
         self.steps = 0
+        self._push_lr()
 
     # -- torch.optim-like surface
     @property
     def lr(self):
         return self.param_groups[0]["lr"]
 
+    def effective_lr(self) -> float:
+        """The rate the update kernels apply in the step about to run: the base rate, for Adam times the bias
+        correction sqrt(1 - beta2^t) / (1 - beta1^t) of step t = steps + 1."""
+        lr = self.param_groups[0]["lr"]
+        if self.rule == "adam":
+            t = self.steps + 1
+            lr = lr * math.sqrt(1.0 - self.hyper["beta2"] ** t) / (1.0 - self.hyper["beta1"] ** t)
+        return lr
+
+    def _push_lr(self):
+        eff = float(self.effective_lr())
+        if self.lr_dev is not None and eff != self._lr_dev_value:
+            self.lr_dev.fill_(eff)
+            self._lr_dev_value = eff
+
     def set_lr(self, lr: float):
         """Change the learning rate (host copy and the device scalar the kernels read)."""
-        lr = float(lr)
-        if lr != self.param_groups[0]["lr"]:
-            self.param_groups[0]["lr"] = lr
-            if self.lr_dev is not None:
-                self.lr_dev.fill_(lr)
+        self.param_groups[0]["lr"] = float(lr)
+        self._push_lr()
 
     def apply_schedule(self):
-        """Set the rate for the step about to run from ``lr_schedule(step)`` (utils/lr_schedule.py), if one is set."""
-        if self.lr_schedule is None:
-            return
+        """Set the rate for the step about to run: ``lr_schedule(step)`` (utils/lr_schedule.py) if one is set, and the
+        device scalar the kernels read (which for Adam changes every step with the bias correction)."""
         if self.master.is_cuda and torch.cuda.is_current_stream_capturing():
             return      # a fill captured into the graph would reset the rate on every replay; the caller sets it outside
-        self.set_lr(self.lr_schedule(self.steps))
+        if self.lr_schedule is not None:
+            self.param_groups[0]["lr"] = float(self.lr_schedule(self.steps))
+        self._push_lr()
 
     def lars_tables(self, block: int):
         """(per-block partial-norm buffer, first block of each tensor, blocks of each tensor), in units of ``block``
@@ -170,7 +201,10 @@ class MomentumSGD:
         lr, mu, wd = g["lr"], g["momentum"], g["weight_decay"]
         if self.master.is_cuda:
             from ..ops import b200_optim
-            b200_optim.sgd_update(self, lo, hi, lr, mu, wd, grad_scale)
+            if self.rule == "momentum":
+                b200_optim.sgd_update(self, lo, hi, lr, mu, wd, grad_scale)
+            else:
+                b200_optim.adaptive_update(self, lo, hi, lr, wd, grad_scale)
             return
         self._update_range_torch(lo, hi, lr, mu, wd, grad_scale)
 
@@ -183,6 +217,23 @@ class MomentumSGD:
             tc = t.clamp(min=0)
             dec = (self.tensor_decay[tc] * valid).repeat_interleave(ALIGN_ELEMS)
             geff = g * grad_scale + wd * dec * w
+            if self.rule != "momentum":
+                h, s2 = self.hyper, self.state2[lo:hi]
+                live = valid.repeat_interleave(ALIGN_ELEMS) > 0       # padding between tensors stays untouched
+                if self.rule == "rmsprop":
+                    s2n = h["rho"] * s2 + (1.0 - h["rho"]) * geff * geff
+                    mn = mu * m + lr * geff / torch.sqrt(s2n + h["eps"])
+                    wn = w - mn
+                else:
+                    mn = h["beta1"] * m + (1.0 - h["beta1"]) * geff
+                    s2n = h["beta2"] * s2 + (1.0 - h["beta2"]) * geff * geff
+                    wn = w - self.effective_lr() * mn / (torch.sqrt(s2n) + h["eps"])
+                s2.copy_(torch.where(live, s2n, s2))
+                m.copy_(torch.where(live, mn, m))
+                w.copy_(torch.where(live, wn, w))
+                if self.shadow is not None:
+                    self.shadow[lo:hi].copy_(w)
+                return
             if self.lars:
                 tr = torch.where(self.tensor_lars[tc] > 0, self.trust[tc], torch.ones_like(self.trust[tc]))
                 geff = geff * tr.repeat_interleave(ALIGN_ELEMS)
@@ -222,31 +273,47 @@ class MomentumSGD:
 
     # -- state
     def state_dict(self):
-        return {"master": self.master.detach().cpu().clone(), "momentum": self.mom.detach().cpu().clone(),
-                "steps": self.steps, "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}],
+        extra = {"state2": self.state2.detach().cpu().clone()} if self.state2 is not None else {}
+        return {"master": self.master.detach().cpu().clone(), "momentum": self.mom.detach().cpu().clone(), **extra,
+                "rule": self.rule, "steps": self.steps, "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}],
                 "plan_hash": self.plan.hash}
 
     def load_state_dict(self, sd):
         if sd.get("plan_hash") not in (None, self.plan.hash):
             raise ValueError("optimizer state was saved with a different fusion plan")
+        if sd.get("rule", "momentum") != self.rule:
+            raise ValueError(f"optimizer state was saved by a {sd.get('rule')} optimizer, this one is {self.rule}")
         with torch.no_grad():
             self.master.copy_(sd["master"])
             self.mom.copy_(sd["momentum"])
+            if self.state2 is not None:
+                self.state2.copy_(sd["state2"])
             if self.shadow is not None:
                 self.shadow.copy_(self.master)
         self.steps = sd.get("steps", 0)
         self.param_groups[0].update(sd["param_groups"][0])
-        if self.lr_dev is not None:
-            self.lr_dev.fill_(float(self.param_groups[0]["lr"]))
+        self._lr_dev_value = None
+        self._push_lr()
 
     def momentum_of(self, p) -> torch.Tensor:
         s, n = self.ranges[p.flat_index]
         return _physical_view(self.mom[s:s + n], p)
 
+    def slots_of(self, p) -> dict:
+        """Optimizer slot variables of parameter ``p`` under their TensorFlow slot names (checkpoints, utils/tfnames.py)."""
+        s, n = self.ranges[p.flat_index]
+        first = _physical_view(self.mom[s:s + n], p)
+        if self.rule == "momentum":
+            return {"Momentum": first}
+        second = _physical_view(self.state2[s:s + n], p)
+        if self.rule == "rmsprop":
+            return {"RMSProp": second, "RMSProp_1": first}        # TF: slot "rms" -> <var>/RMSProp, "momentum" -> /RMSProp_1
+        return {"Adam": first, "Adam_1": second}
+
     def broadcast_state(self, root_rank: int = 0):
         from . import symmetric_context
         ctx = symmetric_context()
-        for t in (self.master, self.mom):
+        for t in (self.master, self.mom) + ((self.state2,) if self.state2 is not None else ()):
             if ctx is not None and t.is_cuda:
                 ctx.broadcast_tensor_(t, root_rank)      # own NVLink broadcast kernel, no NCCL
             else:
@@ -261,6 +328,16 @@ class MomentumSGD:
 
 def LARS(params, lr, momentum=0.9, weight_decay=0.0, eta=0.001, **kw):
     return MomentumSGD(params, lr, momentum, weight_decay, lars=True, lars_eta=eta, **kw)
+
+
+def RMSProp(params, lr, momentum=0.9, weight_decay=0.0, rho=0.9, eps=1.0, **kw):
+    """TF ``RMSPropOptimizer(lr, decay=0.9, momentum=0.9, epsilon=1.0)`` as tf_cnn_benchmarks builds it, on flat buffers."""
+    return MomentumSGD(params, lr, momentum, weight_decay, rule="rmsprop", hyper={"rho": rho, "eps": eps}, **kw)
+
+
+def Adam(params, lr, weight_decay=0.0, beta1=0.9, beta2=0.999, eps=1e-8, **kw):
+    """TF ``AdamOptimizer(lr, 0.9, 0.999, 1e-8)`` on flat buffers."""
+    return MomentumSGD(params, lr, 0.0, weight_decay, rule="adam", hyper={"beta1": beta1, "beta2": beta2, "eps": eps}, **kw)
 
 
 class DistributedOptimizer:
@@ -431,9 +508,14 @@ class DistributedOptimizer:
             ev[1].record(self._comm_stream)
         if self.fused and self._symm is not None:
             with torch.cuda.stream(self._comm_stream):
-                # one launch per bucket either way; LARS folds the norms of the tensors that end in this bucket
-                lars = self._opt.lars_bucket_args(b, self._symm.block) if self._opt.lars else None
-                self._symm.fused_allreduce_sgd(self._symm_grad, self._opt, lo, hi, scale, lars=lars)
+                if self._opt.rule != "momentum":
+                    # RMSProp / Adam: own NVLink allreduce of the bucket, then the flat update kernel behind it
+                    self._symm.allreduce_range_(self._symm_grad, lo, hi, scale)
+                    self._opt.update_range(lo, hi, 1.0)
+                else:
+                    # one launch per bucket either way; LARS folds the norms of the tensors that end in this bucket
+                    lars = self._opt.lars_bucket_args(b, self._symm.block) if self._opt.lars else None
+                    self._symm.fused_allreduce_sgd(self._symm_grad, self._opt, lo, hi, scale, lars=lars)
             self._handles.append((b, None, scale))
         else:
             chunk = self.grad[lo:hi]

@@ -17,6 +17,24 @@ def sgd_update(opt, lo: int, hi: int, lr: float, mu: float, wd: float, grad_scal
                                         _ptr(getattr(opt, "lr_dev", None)), _stream()), "sgd_momentum_flat")
 
 
+def adaptive_update(opt, lo: int, hi: int, lr: float, wd: float, grad_scale: float):
+    """RMSProp / Adam (opt.rule) on flat elements [lo, hi): one launch (csrc/kernels/optim.cu adaptive_flat_kernel).
+    Reference role: TF ApplyRMSProp / ApplyAdam under --optimizer=rmsprop|adam (the flag at run-tf-sing-ucx-openmpi.sh:73)."""
+    if hi <= lo:
+        return
+    blk = opt.block_tensor[lo // 1024:]
+    shadow = opt.shadow[lo:] if opt.shadow is not None else None
+    h = opt.hyper
+    common = (_ptr(opt.master[lo:]), _ptr(opt.mom[lo:]), _ptr(opt.state2[lo:]), _ptr(opt.grad[lo:]), _ptr(shadow), hi - lo,
+              _ptr(blk), _ptr(opt.tensor_decay))
+    if opt.rule == "rmsprop":
+        _check(lib().b200_rmsprop_flat(*common, lr, h["rho"], opt.param_groups[0]["momentum"], h["eps"], wd, grad_scale,
+                                       _ptr(opt.lr_dev), _stream()), "rmsprop_flat")
+    else:
+        _check(lib().b200_adam_flat(*common, opt.effective_lr(), h["beta1"], h["beta2"], h["eps"], wd, grad_scale,
+                                    _ptr(opt.lr_dev), _stream()), "adam_flat")
+
+
 def lars_trust(opt, wd: float, grad_scale: float):
     import torch
     if not hasattr(opt, "_lars_blk"):

@@ -47,6 +47,8 @@ def w_dist_opt(rank, world, mode, steps):
         base = hvd.MomentumSGD(named, lr=0.05, momentum=0.9, weight_decay=1e-3, fusion_threshold=8192)
     elif mode == "lars":
         base = hvd.LARS(named, lr=0.05, momentum=0.9, weight_decay=1e-3, eta=0.01, fusion_threshold=8192)
+    elif mode in ("rmsprop", "adam"):
+        base = _adaptive(hvd, mode, named, fusion_threshold=8192)
     else:
         base = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3)
     opt = hvd.DistributedOptimizer(base, named_parameters=named, fusion_threshold=8192)
@@ -69,6 +71,9 @@ def single_process_reference(world, mode, steps):
     if mode == "lars":
         from .. import hvd
         opt = hvd.LARS(list(net.named_parameters()), lr=0.05, momentum=0.9, weight_decay=1e-3, eta=0.01)
+    elif mode in ("rmsprop", "adam"):
+        from .. import hvd
+        opt = _adaptive(hvd, mode, list(net.named_parameters()))
     else:
         opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3)
     g = torch.Generator().manual_seed(7)
@@ -79,6 +84,12 @@ def single_process_reference(world, mode, steps):
         ((net(full_x[s]) - full_y[s]) ** 2).mean().backward()
         opt.step()
     return [p.detach().cpu().contiguous() for p in net.parameters()]
+
+
+def _adaptive(hvd, mode, named, **kw):
+    if mode == "rmsprop":
+        return hvd.RMSProp(named, lr=0.01, momentum=0.9, weight_decay=1e-3, **kw)
+    return hvd.Adam(named, lr=0.01, weight_decay=1e-3, **kw)
 
 
 def w_plan_mismatch(rank, world):
@@ -203,11 +214,15 @@ def w_nvl_fused_training(rank, world, steps, lars):
     dev = hvd.device()
     net = _net(dev)
     named = list(net.named_parameters())
-    mk = hvd.LARS if lars else hvd.MomentumSGD
-    kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-3, fusion_threshold=8192)
-    if lars:
-        kw["eta"] = 0.01
-    opt = hvd.DistributedOptimizer(mk(named, **kw), named_parameters=named)
+    if lars in ("rmsprop", "adam"):        # own allreduce kernel + flat RMSProp / Adam kernel per bucket
+        inner = _adaptive(hvd, lars, named, fusion_threshold=8192)
+    else:
+        mk = hvd.LARS if lars else hvd.MomentumSGD
+        kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-3, fusion_threshold=8192)
+        if lars:
+            kw["eta"] = 0.01
+        inner = mk(named, **kw)
+    opt = hvd.DistributedOptimizer(inner, named_parameters=named)
     hvd.broadcast_parameters(net.state_dict(), root_rank=0)
     hvd.broadcast_optimizer_state(opt, root_rank=0)
     g = torch.Generator().manual_seed(7)

@@ -70,24 +70,26 @@ def variables(model, optimizer=None, global_step: int = 0) -> Dict[str, torch.Te
     out: Dict[str, torch.Tensor] = {}
     for name, p in named_tf_parameters(model):
         out[name] = to_tf_layout(p.detach().float().cpu(), p.tf_layout)
-        if optimizer is not None:
-            mom = _momentum_of(optimizer, p)
-            if mom is not None:
-                out[f"{name}/{MOMENTUM_SLOT}"] = to_tf_layout(mom.detach().float().cpu(), p.tf_layout)
+        for slot, t in _slots_of(optimizer, p).items():
+            out[f"{name}/{slot}"] = to_tf_layout(t.detach().float().cpu(), p.tf_layout)
     for name, buf, _m, _a in named_tf_buffers(model):
         out[name] = buf.detach().float().cpu().clone()
     out[GLOBAL_STEP] = torch.tensor(int(global_step), dtype=torch.int64)
     return out
 
 
-def _momentum_of(optimizer, p):
+def _slots_of(optimizer, p) -> Dict[str, torch.Tensor]:
+    """Optimizer slot variables of ``p`` keyed by TF slot name: ``Momentum`` (MomentumOptimizer), ``RMSProp`` /
+    ``RMSProp_1`` (RMSPropOptimizer's rms and momentum), ``Adam`` / ``Adam_1`` (m and v)."""
+    if optimizer is None:
+        return {}
     opt = getattr(optimizer, "_opt", optimizer)
-    if hasattr(opt, "momentum_of"):
-        return opt.momentum_of(p) if hasattr(p, "flat_index") else None
+    if hasattr(opt, "slots_of"):
+        return opt.slots_of(p) if hasattr(p, "flat_index") else {}
     st = getattr(opt, "state", {}).get(p)
-    if st:
-        return st.get("momentum_buffer")
-    return None
+    if st and st.get("momentum_buffer") is not None:
+        return {MOMENTUM_SLOT: st["momentum_buffer"]}
+    return {}
 
 
 def assign(model, optimizer, values: Dict[str, torch.Tensor]) -> int:
@@ -99,11 +101,9 @@ def assign(model, optimizer, values: Dict[str, torch.Tensor]) -> int:
                 missing.append(name)
                 continue
             p.copy_(from_tf_layout(torch.as_tensor(values[name]), p.tf_layout).to(p.dtype))
-            mname = f"{name}/{MOMENTUM_SLOT}"
-            if optimizer is not None and mname in values:
-                mom = _momentum_of(optimizer, p)
-                if mom is not None:
-                    mom.copy_(from_tf_layout(torch.as_tensor(values[mname]), p.tf_layout).to(mom.dtype))
+            for slot, t in _slots_of(optimizer, p).items():
+                if f"{name}/{slot}" in values:
+                    t.copy_(from_tf_layout(torch.as_tensor(values[f"{name}/{slot}"]), p.tf_layout).to(t.dtype))
         for name, buf, _m, _a in named_tf_buffers(model):
             if name in values:
                 buf.copy_(torch.as_tensor(values[name]).to(buf.dtype))

@@ -40,6 +40,18 @@ int b200_sgd_momentum_flat(float* master, float* mom, const float* grad, b200_bf
                            const float* trust, float lr, float mu, float wd, float grad_scale, const float* lr_dev,
                            void* stream);
 
+/* RMSProp / Adam on the same flat buffers, TensorFlow update rules (tf_cnn_benchmarks --optimizer=rmsprop|adam):
+ *   rmsprop: ms = rho*ms + (1-rho)*g^2; mom = mu*mom + lr*g/sqrt(ms+eps); w -= mom      (ms starts at 1, mom at 0)
+ *   adam:    m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2; w -= lr_t*m/(sqrt(v)+eps), lr_t = lr*sqrt(1-b2^t)/(1-b1^t)
+ * g = grad*grad_scale + wd*decay[tensor]*w. lr_dev (optional) overrides lr / lr_t from device memory (schedules and the
+ * Adam bias correction under a captured CUDA graph). Same block table and bf16 shadow as b200_sgd_momentum_flat. */
+int b200_rmsprop_flat(float* master, float* mom, float* ms, const float* grad, b200_bf16* shadow, int64_t n,
+                      const int32_t* block_tensor, const float* tensor_decay, float lr, float rho, float mu, float eps,
+                      float wd, float grad_scale, const float* lr_dev, void* stream);
+int b200_adam_flat(float* master, float* m, float* v, const float* grad, b200_bf16* shadow, int64_t n,
+                   const int32_t* block_tensor, const float* tensor_decay, float lr_t, float beta1, float beta2, float eps,
+                   float wd, float grad_scale, const float* lr_dev, void* stream);
+
 /* LARS: per-tensor squared norms of w and grad*grad_scale over a flat range → norms[2t], norms[2t+1]
  * (norms must be zeroed by the caller), then trust[t] = eta*|w| / (|g| + wd*decay[t]*|w| + eps) for tensors
  * with tensor_lars[t] != 0, else 1. No reference counterpart beyond the product definition (BASELINE.json). */

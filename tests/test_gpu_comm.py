@@ -36,7 +36,7 @@ def test_flag_protocol_stress_with_random_delays():
 
 
 @needs2
-@pytest.mark.parametrize("lars", [False, True])
+@pytest.mark.parametrize("lars", [False, True, "rmsprop", "adam"])
 def test_fused_allreduce_sgd_training_matches_single_process(lars):
     from azure_hc_intel_tf_b200.utils import testing, testing_workers as W
     world = 2
@@ -45,7 +45,7 @@ def test_fused_allreduce_sgd_training_matches_single_process(lars):
     assert used0 and used1 and nb > 1
     for a, b in zip(w0, w1):
         assert torch.equal(a, b)
-    ref = W.single_process_reference(world, "lars" if lars else "fused", 4)
+    ref = W.single_process_reference(world, lars if isinstance(lars, str) else ("lars" if lars else "fused"), 4)
     for a, r in zip(w0, ref):
         assert torch.allclose(a, r, atol=5e-6, rtol=2e-4)
 

@@ -191,6 +191,30 @@ def test_flat_sgd_kernel_matches_cpu_oracle(lars):
     assert torch.equal(og.shadow, og.master.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("rule", ["rmsprop", "adam"])
+def test_flat_rmsprop_adam_kernels_match_cpu_oracle(rule):
+    """adaptive_flat_kernel (TF ApplyRMSProp / ApplyAdam rules) vs the plain-PyTorch oracle of the same optimizer on CPU;
+    the Adam bias correction travels through the device scalar lr_dev."""
+    from azure_hc_intel_tf_b200 import hvd
+    cpu_net, gpu_net = _small_net(), _small_net().to(DEV)
+    mk = hvd.RMSProp if rule == "rmsprop" else hvd.Adam
+    kw = dict(lr=0.01, weight_decay=1e-3, fusion_threshold=16384, lowp=True)
+    oc, og = mk(list(cpu_net.named_parameters()), **kw), mk(list(gpu_net.named_parameters()), **kw)
+    x = torch.randn(4, 3, 8, 8)
+    for _ in range(4):
+        for net, opt, xx in ((cpu_net, oc, x), (gpu_net, og, x.to(DEV))):
+            opt.zero_grad()
+            net(xx).square().mean().backward()
+            opt.step()
+    assert abs(float(og.lr_dev) - og._lr_dev_value) < 1e-9 and og.steps == 4
+    if rule == "adam":
+        assert abs(og._lr_dev_value - 0.01 * (1 - 0.999 ** 4) ** 0.5 / (1 - 0.9 ** 4)) < 1e-9     # rate of the last step run
+    assert torch.allclose(oc.master, og.master.cpu(), atol=2e-5, rtol=1e-3)
+    assert torch.allclose(oc.mom, og.mom.cpu(), atol=2e-5, rtol=1e-3)
+    assert torch.allclose(oc.state2, og.state2.cpu(), atol=2e-5, rtol=1e-3)
+    assert torch.equal(og.shadow, og.master.to(torch.bfloat16))
+
+
 @pytest.mark.parametrize("model,batch", [("resnet50", 8), ("vgg11", 4), ("googlenet", 4)])
 def test_model_b200_path_matches_library_path(model, batch):
     """Whole-model parity from the same weights and input: the b200 ops layer (own conv/BN/pool/loss kernels)

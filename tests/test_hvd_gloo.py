@@ -14,7 +14,7 @@ def test_api_basics_ws2():
         assert obj == {"r": 0}
 
 
-@pytest.mark.parametrize("mode", ["fused", "generic", "lars"])
+@pytest.mark.parametrize("mode", ["fused", "generic", "lars", "rmsprop", "adam"])
 def test_distributed_optimizer_matches_single_process(mode):
     steps = 4
     outs = testing.run_ranks(W.w_dist_opt, 2, "gloo", args=(mode, steps))
