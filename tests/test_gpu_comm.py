@@ -46,8 +46,13 @@ def test_fused_allreduce_sgd_training_matches_single_process(lars):
     for a, b in zip(w0, w1):
         assert torch.equal(a, b)
     ref = W.single_process_reference(world, lars if isinstance(lars, str) else ("lars" if lars else "fused"), 4)
+    # Adam's first steps move every weight by about lr * sign(g): rounding-level differences in near-zero gradients
+    # (GPU vs CPU convolution, reduction order) are amplified to a fraction of lr = 0.01, so its bound is on that scale
+    tol = dict(atol=2e-3, rtol=1e-2) if lars == "adam" else dict(atol=5e-6, rtol=2e-4)
     for a, r in zip(w0, ref):
-        assert torch.allclose(a, r, atol=5e-6, rtol=2e-4)
+        assert torch.allclose(a, r, **tol), float((a - r).abs().max())
+        if lars == "adam":
+            assert float((a - r).abs().median()) < 2e-5
 
 
 @needs2
