@@ -43,6 +43,8 @@ SIGS = {
     "b200_normalize_u8": (i32, [vp, vp, i64, i32, i32, vp]),
     "b200_add": (i32, [vp, vp, vp, i64, vp]),
     "b200_add_masked": (i32, [vp, vp, vp, vp, i64, vp]),
+    "b200_add_act": (i32, [vp, vp, vp, i64, i32, vp]),
+    "b200_relu_bwd": (i32, [vp, vp, vp, i64, vp]),
     "b200_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
 }
 

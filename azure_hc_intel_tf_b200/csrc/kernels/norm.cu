@@ -522,6 +522,40 @@ __global__ void __launch_bounds__(256) add_masked_kernel(const b200_bf16* __rest
   }
 }
 
+// o = relu(a + b): the standalone residual sum of the CIFAR ResNets and pre-activation models (blocks whose sum is not
+// behind a batch-norm, so it cannot ride in bn_apply); relu == 0 gives the plain sum.
+__global__ void __launch_bounds__(256) add_act_kernel(const b200_bf16* __restrict__ a, const b200_bf16* __restrict__ b,
+                                                      b200_bf16* __restrict__ o, int64_t nvec, int relu) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < nvec; i += stride) {
+    float x[8], y[8];
+    unpack8(ld8_stream(a + i * 8), x);
+    unpack8(ld8_stream(b + i * 8), y);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      x[k] += y[k];
+      if (relu) x[k] = fmaxf(x[k], 0.0f);
+    }
+    st8(o + i * 8, pack8(x));
+  }
+}
+
+// dx = z > 0 ? dz : 0 (backward of the ReLU above, gated by its output)
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const b200_bf16* __restrict__ dz, const b200_bf16* __restrict__ z,
+                                                       b200_bf16* __restrict__ dx, int64_t nvec) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < nvec; i += stride) {
+    float g[8], v[8];
+    unpack8(ld8_stream(dz + i * 8), g);
+    unpack8(ld8_stream(z + i * 8), v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = v[k] > 0.0f ? g[k] : 0.0f;
+    st8(dx + i * 8, pack8(g));
+  }
+}
+
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, b200_bf16* __restrict__ y, int64_t n) {
   int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
@@ -641,6 +675,20 @@ int b200_add_masked(const b200_bf16* a, const b200_bf16* b, const uint8_t* mask,
                     void* stream) {
   B200_CHECK_ARG(a && b && mask && out && n % 8 == 0, "add_masked: need n%%8==0");
   add_masked_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, mask, out, n / 8);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_add_act(const b200_bf16* a, const b200_bf16* b, b200_bf16* out, int64_t n, int32_t relu, void* stream) {
+  B200_CHECK_ARG(a && b && out && n > 0 && n % 8 == 0, "add_act: need n%%8==0");
+  add_act_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, out, n / 8, relu);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_relu_bwd(const b200_bf16* dz, const b200_bf16* z, b200_bf16* dx, int64_t n, void* stream) {
+  B200_CHECK_ARG(dz && z && dx && n > 0 && n % 8 == 0, "relu_bwd: need n%%8==0");
+  relu_bwd_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dz, z, dx, n / 8);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -48,7 +48,7 @@ class BottleneckV2(nn.Module):
             sc = x
         else:
             sc = self.shortcut(pre if self.shortcut_from_preact else x)
-        return sc + self.conv3(self.conv2(self.conv1(pre)))
+        return ops.add(sc, self.conv3(self.conv2(self.conv1(pre))), self.cfg)
 
 
 class ResNetV2(Model):
@@ -116,7 +116,7 @@ class ResidualBlockCifar(nn.Module):
             sc = sc.contiguous(memory_format=torch.channels_last)
         h = self.preact(x) if self.v2 else x
         y = self.conv2(self.conv1(h))
-        return sc + y if self.v2 else ops.add_relu(sc, y, self.cfg)
+        return ops.add(sc, y, self.cfg) if self.v2 else ops.add_relu(sc, y, self.cfg)
 
 
 class ResNetCifar(Model):

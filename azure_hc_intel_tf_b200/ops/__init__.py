@@ -135,6 +135,13 @@ def add_relu(a, b, cfg):
     return F.relu(a + b, inplace=True)
 
 
+def add(a, b, cfg):
+    """Residual sum without activation (pre-activation ResNets)."""
+    if cfg.kernels == "b200":
+        return _b200().add_act(a, b, False)
+    return a + b
+
+
 def concat_channels(xs):
     # channels_last tensors: the concat is a strided copy into the channel-interleaved output.
     return torch.cat(xs, dim=1)

@@ -476,10 +476,42 @@ def spatial_mean(x):
     return _SpatialMean.apply(x)
 
 
+class _AddAct(torch.autograd.Function):
+    """act(a + b) outside a conv block: the residual sum of the CIFAR ResNets (ReLU) and of the pre-activation models
+    (no activation). ResNet v1's sum rides in bn_apply (conv_block(residual=...)); this is for blocks whose sum is not
+    behind a batch-norm. Reference role: the Add / Relu ops MKL-DNN fuses under --mkl=TRUE (run-tf-sing-ucx-openmpi.sh:76)."""
+
+    @staticmethod
+    def forward(ctx, a, b, relu):
+        a, b = nhwc(a), nhwc(b)
+        n, c, h, w = a.shape
+        z = empty_nhwc(n, c, h, w, a.device)
+        _check(lib().b200_add_act(_ptr(a), _ptr(b), _ptr(z), a.numel(), int(relu), _stream()), "add_act")
+        ctx.relu = relu
+        if relu:
+            ctx.save_for_backward(z)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        if not ctx.relu:
+            return dz, dz, None
+        (z,) = ctx.saved_tensors
+        dz = nhwc(dz)
+        n, c, h, w = dz.shape
+        dx = empty_nhwc(n, c, h, w, dz.device)
+        _check(lib().b200_relu_bwd(_ptr(dz), _ptr(z), _ptr(dx), dz.numel(), _stream()), "relu_bwd")
+        return dx, dx, None
+
+
+def add_act(a, b, relu):
+    if a.dim() != 4 or a.shape != b.shape or a.numel() % 8 or a.shape[1] % 8:
+        return torch.relu_(a + b) if relu else a + b          # shapes the 8-channel vectors do not cover
+    return _AddAct.apply(a, b, bool(relu))
+
+
 def add_relu(a, b):
-    """relu(a + b) outside a conv block (the residual add of ResNet is fused into conv_block(residual=...));
-    plain tensor ops: nothing in the model zoo reaches this on the kernel path."""
-    return torch.relu_(a + b)
+    return add_act(a, b, True)
 
 
 # ------------------------------------------------------------------------------------ loss / input

@@ -181,6 +181,10 @@ int b200_add(const b200_bf16* a, const b200_bf16* b, b200_bf16* out, int64_t n, 
  * block-output ReLU, without materialising the gated copy. n % 8 == 0. */
 int b200_add_masked(const b200_bf16* a, const b200_bf16* b, const uint8_t* mask, b200_bf16* out, int64_t n,
                     void* stream);
+/* out = relu ? max(a + b, 0) : a + b - the residual sum of blocks whose sum is not behind a batch-norm (CIFAR ResNets,
+ * pre-activation ResNets); b200_relu_bwd: dx = z > 0 ? dz : 0 with z the output above. n % 8 == 0, in place allowed. */
+int b200_add_act(const b200_bf16* a, const b200_bf16* b, b200_bf16* out, int64_t n, int32_t relu, void* stream);
+int b200_relu_bwd(const b200_bf16* dz, const b200_bf16* z, b200_bf16* dx, int64_t n, void* stream);
 /* fp32 → bf16 cast of n elements. */
 int b200_cast_f32_bf16(const float* x, b200_bf16* y, int64_t n, void* stream);
 

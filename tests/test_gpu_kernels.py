@@ -191,6 +191,30 @@ def test_flat_sgd_kernel_matches_cpu_oracle(lars):
     assert torch.equal(og.shadow, og.master.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("relu", [False, True])
+def test_standalone_residual_add_node(relu):
+    """add_act_kernel / relu_bwd_kernel (the residual sum of the CIFAR and pre-activation ResNets) vs fp32 PyTorch."""
+    from azure_hc_intel_tf_b200.ops import b200
+    g = torch.Generator().manual_seed(3)
+    mk = lambda: torch.randn(4, 9, 7, 24, generator=g).to(DEV).to(torch.bfloat16).permute(0, 3, 1, 2).requires_grad_(True)
+    a, b = mk(), mk()
+    before = b200.launch_count
+    z = b200.add_act(a, b, relu)
+    dz = torch.randn(4, 9, 7, 24, generator=g).to(DEV).to(torch.bfloat16).permute(0, 3, 1, 2)
+    z.backward(dz)
+    assert b200.launch_count - before == (2 if relu else 1)          # own kernels ran, not the eager fallback
+    af, bf = a.detach().float().requires_grad_(True), b.detach().float().requires_grad_(True)
+    zr = af + bf
+    if relu:
+        zr = torch.relu(zr)
+    zr.backward(dz.float())
+    assert torch.allclose(z.float(), zr, atol=2e-2, rtol=1e-2)
+    assert torch.equal(a.grad, b.grad)
+    # the gate is taken from the stored (bf16-rounded) output, like the oracle's up to rounding of values next to zero
+    agree = (a.grad.float() == af.grad).float().mean().item()
+    assert agree > 0.999, agree
+
+
 @pytest.mark.parametrize("rule", ["rmsprop", "adam"])
 def test_flat_rmsprop_adam_kernels_match_cpu_oracle(rule):
     """adaptive_flat_kernel (TF ApplyRMSProp / ApplyAdam rules) vs the plain-PyTorch oracle of the same optimizer on CPU;
