@@ -4,7 +4,8 @@
 // (benchmark-scripts/run-tf-sing-ucx-openmpi.sh:76), reached when --model (:66) selects MobileNet. A depthwise layer
 // does R*S multiply-adds per output element and reads every input once: it is bandwidth-bound, there is no GEMM in it,
 // so these are plain vector kernels (8 channels = one 16-byte vector per thread, filter taps in registers), not
-// tensor-core kernels. Filters are [C][R][S] (the KRSC layout of a [C,1,R,S] weight), R*S <= 9.
+// tensor-core kernels. Filters are [C][R][S] (the KRSC layout of a [C,1,R,S] weight), up to 7x7; 3x3 at stride 1 / 2
+// (every MobileNet layer) has a fast path, everything else (NASNet's 5x5 / 7x7) the generic kernels.
 #include "b200conv.h"
 #include "common.cuh"
 
@@ -14,137 +15,166 @@
 namespace b200 {
 namespace {
 
-constexpr int kMaxTaps = 9;
+constexpr int kMaxTaps = 49, kMaxS = 7;      // generic kernels: filters up to 7x7
+constexpr int kGenCvecs = 32;                 // 8-channel vectors per block of the generic kernels
 
 struct DwGeom {
   int n, h, w, c, r, s, p, q, sh, sw, pt, pl;
 };
 
-// thread (tx, ty): tx walks the 8-channel vectors, ty the pixels; a thread's channels are fixed for its lifetime when
-// cvecs <= blockDim.x (every MobileNet layer), so the taps are loaded into registers once
-__device__ __forceinline__ void load_taps(const b200_bf16* __restrict__ w, int c0, int taps, float wt[kMaxTaps][8]) {
+// acc += a.half[ha] * b.half[hb]: mixed-precision FMA with the bf16 operands taken in place from the packed registers
+// (PTX fma.rn.f32.bf16 = SASS FHFMA.BF16 with .H0/.H1 operand selectors on sm_100a) - exact product, one rounding, so
+// it equals an fp32 FMA of the converted values without spending instructions on the conversions. ha / hb are
+// compile-time constants at every call (fully unrolled loops), so one of the four forms survives.
+__device__ __forceinline__ void fma_bf16(float& acc, uint32_t a, int ha, uint32_t b, int hb) {
+  if (ha == 0 && hb == 0)
+    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, al, bl, %0; }" : "+f"(acc) : "r"(a), "r"(b));
+  else if (ha == 0)
+    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, al, bh, %0; }" : "+f"(acc) : "r"(a), "r"(b));
+  else if (hb == 0)
+    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, ah, bl, %0; }" : "+f"(acc) : "r"(a), "r"(b));
+  else
+    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, ah, bh, %0; }" : "+f"(acc) : "r"(a), "r"(b));
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Generic kernels (any filter up to 7x7, any stride: NASNet's 5x5 / 7x7 separable convolutions, 2x2 filters, ...).
+// Block = (up to 32 channel vectors, pixels); gridDim.y walks the channel chunks. The block's filter taps are staged
+// once in shared memory as [tap][channel vector] 16-byte words, so a thread reads one input vector and one tap vector
+// per tap and feeds both packed words to FHFMA.BF16.
+
+// taps of channels [c0, c0 + 8 * nvec) -> smem [tap][vec] (uint4 = 8 bf16); all threads of the block take part
+__device__ __forceinline__ void stage_taps(const b200_bf16* __restrict__ w, int c0, int nvec, int taps, uint4* wsm) {
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
+  for (int e = tid; e < taps * nvec; e += nthr) {
+    const int t = e / nvec, v = e - t * nvec;
+    uint32_t pk[4];
 #pragma unroll
-  for (int t = 0; t < kMaxTaps; ++t)
+    for (int k2 = 0; k2 < 4; ++k2) {
+      const uint32_t lo = w[(size_t)(c0 + v * 8 + 2 * k2) * taps + t], hi = w[(size_t)(c0 + v * 8 + 2 * k2 + 1) * taps + t];
+      pk[k2] = lo | (hi << 16);
+    }
+    wsm[t * kGenCvecs + v] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void fma_vec8(float acc[8], const uint4& a, const uint4& b) {
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int k = 0; k < 8; ++k)
-      wt[t][k] = t < taps ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(w)[(size_t)(c0 + k) * taps + t]) : 0.0f;
+  for (int k = 0; k < 8; ++k) fma_bf16(acc[k], aw[k >> 1], k & 1, bw[k >> 1], k & 1);
 }
 
 __global__ void __launch_bounds__(256) dw_fwd_kernel(const b200_bf16* __restrict__ x, const b200_bf16* __restrict__ w,
                                                      b200_bf16* __restrict__ y, DwGeom g) {
+  __shared__ uint4 wsm[kMaxTaps * kGenCvecs];
   const int cvecs = g.c / 8, taps = g.r * g.s;
+  const int cv0 = blockIdx.y * kGenCvecs, nvec = min(kGenCvecs, cvecs - cv0);
+  stage_taps(w, cv0 * 8, nvec, taps, wsm);
+  if ((int)threadIdx.x >= nvec) return;
+  const int cv = cv0 + threadIdx.x;
   const int64_t pixels = (int64_t)g.n * g.p * g.q;
-  for (int cv = threadIdx.x; cv < cvecs; cv += blockDim.x) {
-    float wt[kMaxTaps][8];
-    load_taps(w, cv * 8, taps, wt);
-    for (int64_t pix = (int64_t)blockIdx.x * blockDim.y + threadIdx.y; pix < pixels; pix += (int64_t)gridDim.x * blockDim.y) {
-      const int q = (int)(pix % g.q);
-      const int p = (int)((pix / g.q) % g.p);
-      const int n = (int)(pix / ((int64_t)g.q * g.p));
-      float acc[8];
+  for (int64_t pix = (int64_t)blockIdx.x * blockDim.y + threadIdx.y; pix < pixels; pix += (int64_t)gridDim.x * blockDim.y) {
+    const int q = (int)(pix % g.q);
+    const int p = (int)((pix / g.q) % g.p);
+    const int n = (int)(pix / ((int64_t)g.q * g.p));
+    float acc[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+    for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+    for (int r = 0; r < g.r; ++r) {
+      const int ih = p * g.sh - g.pt + r;
+      if (ih < 0 || ih >= g.h) continue;
+      const b200_bf16* xr = x + ((size_t)(n * g.h + ih) * g.w) * g.c + cv * 8;
 #pragma unroll
-      for (int t = 0; t < kMaxTaps; ++t) {
-        if (t >= taps) break;
-        const int r = t / g.s, s = t - r * g.s;
-        const int ih = p * g.sh - g.pt + r, iw = q * g.sw - g.pl + s;
-        if (ih < 0 || ih >= g.h || iw < 0 || iw >= g.w) continue;
-        float f[8];
-        unpack8(ld8(x + (((size_t)n * g.h + ih) * g.w + iw) * g.c + cv * 8), f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = fmaf(f[k], wt[t][k], acc[k]);
+      for (int s = 0; s < kMaxS; ++s) {
+        const int iw = q * g.sw - g.pl + s;
+        if (s < g.s && iw >= 0 && iw < g.w)
+          fma_vec8(acc, __ldg(reinterpret_cast<const uint4*>(xr + (size_t)iw * g.c)), wsm[(r * g.s + s) * kGenCvecs + threadIdx.x]);
       }
-      st8(y + (size_t)pix * g.c + cv * 8, pack8(acc));
     }
+    st8(y + (size_t)pix * g.c + cv * 8, pack8(acc));
   }
 }
 
 // dx[n,h,w,c] = sum over taps (r,s) with (h + pt - r) % sh == 0 and (w + pl - s) % sw == 0 of dy[n, ., ., c] * w[c,r,s]
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(const b200_bf16* __restrict__ dy, const b200_bf16* __restrict__ w,
                                                        b200_bf16* __restrict__ dx, DwGeom g) {
+  __shared__ uint4 wsm[kMaxTaps * kGenCvecs];
   const int cvecs = g.c / 8, taps = g.r * g.s;
+  const int cv0 = blockIdx.y * kGenCvecs, nvec = min(kGenCvecs, cvecs - cv0);
+  stage_taps(w, cv0 * 8, nvec, taps, wsm);
+  if ((int)threadIdx.x >= nvec) return;
+  const int cv = cv0 + threadIdx.x;
   const int64_t pixels = (int64_t)g.n * g.h * g.w;
-  for (int cv = threadIdx.x; cv < cvecs; cv += blockDim.x) {
-    float wt[kMaxTaps][8];
-    load_taps(w, cv * 8, taps, wt);
-    for (int64_t pix = (int64_t)blockIdx.x * blockDim.y + threadIdx.y; pix < pixels; pix += (int64_t)gridDim.x * blockDim.y) {
-      const int iw = (int)(pix % g.w);
-      const int ih = (int)((pix / g.w) % g.h);
-      const int n = (int)(pix / ((int64_t)g.w * g.h));
-      float acc[8];
+  for (int64_t pix = (int64_t)blockIdx.x * blockDim.y + threadIdx.y; pix < pixels; pix += (int64_t)gridDim.x * blockDim.y) {
+    const int iw = (int)(pix % g.w);
+    const int ih = (int)((pix / g.w) % g.h);
+    const int n = (int)(pix / ((int64_t)g.w * g.h));
+    float acc[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+    for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+    for (int r = 0; r < g.r; ++r) {
+      const int a = ih + g.pt - r;
+      if (a < 0 || a % g.sh || a / g.sh >= g.p) continue;
+      const b200_bf16* yr = dy + ((size_t)(n * g.p + a / g.sh) * g.q) * g.c + cv * 8;
 #pragma unroll
-      for (int t = 0; t < kMaxTaps; ++t) {
-        if (t >= taps) break;
-        const int r = t / g.s, s = t - r * g.s;
-        const int a = ih + g.pt - r, b = iw + g.pl - s;
-        if (a < 0 || b < 0 || a % g.sh || b % g.sw) continue;
-        const int p = a / g.sh, q = b / g.sw;
-        if (p >= g.p || q >= g.q) continue;
-        float f[8];
-        unpack8(ld8(dy + (((size_t)n * g.p + p) * g.q + q) * g.c + cv * 8), f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = fmaf(f[k], wt[t][k], acc[k]);
+      for (int s = 0; s < kMaxS; ++s) {
+        const int b = iw + g.pl - s;
+        if (s < g.s && b >= 0 && b % g.sw == 0 && b / g.sw < g.q)
+          fma_vec8(acc, __ldg(reinterpret_cast<const uint4*>(yr + (size_t)(b / g.sw) * g.c)), wsm[(r * g.s + s) * kGenCvecs + threadIdx.x]);
       }
-      st8(dx + (size_t)pix * g.c + cv * 8, pack8(acc));
     }
+    st8(dx + (size_t)pix * g.c + cv * 8, pack8(acc));
   }
 }
 
-// dw[c,r,s] = sum over output pixels of dy[n,p,q,c] * x[n, p*sh - pt + r, q*sw - pl + s, c]. Each thread owns 8 channels
-// and a strided set of pixels and keeps taps x 8 fp32 sums in registers; the block folds its pixel lanes (threadIdx.y)
-// through shared memory in lane order and writes one row of `partials` ([gridDim.x][taps][c]); dw_fold_kernel sums the
-// rows in index order, so the result is bitwise reproducible.
+// dw[c,r,s] = sum over output pixels of dy[n,p,q,c] * x[n, p*sh - pt + r, q*sw - pl + s, c]. gridDim.y = channel chunks
+// x filter rows: a thread owns 8 channels and ONE filter row (up to 7 x 8 fp32 sums in registers) over a strided set of
+// pixels; the block folds its pixel lanes (threadIdx.y) through shared memory in lane order and writes one row of
+// `partials` ([gridDim.x][taps][c]); dw_fold_kernel sums the rows in index order (bitwise reproducible).
 __global__ void __launch_bounds__(256) dw_wgrad_kernel(const b200_bf16* __restrict__ x, const b200_bf16* __restrict__ dy,
                                                        float* __restrict__ partials, DwGeom g) {
   __shared__ float red[256 * 8];
   const int cvecs = g.c / 8, taps = g.r * g.s;
-  const int64_t pixels = (int64_t)g.n * g.p * g.q;
+  const int chunk = blockIdx.y / g.r, r = blockIdx.y - chunk * g.r;
   const int tx = threadIdx.x, ty = threadIdx.y, nx = blockDim.x, ny = blockDim.y;
-  for (int cv0 = 0; cv0 < cvecs; cv0 += nx) {
-    const int cv = cv0 + tx;
-    const bool active = cv < cvecs;
-    float acc[kMaxTaps][8];
+  const int cv = chunk * kGenCvecs + tx;
+  const bool active = tx < kGenCvecs && cv < cvecs;
+  const int64_t pixels = (int64_t)g.n * g.p * g.q;
+  float acc[kMaxS][8];
 #pragma unroll
-    for (int t = 0; t < kMaxTaps; ++t)
+  for (int s = 0; s < kMaxS; ++s)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[t][k] = 0.0f;
-    if (active) {
-      for (int64_t pix = (int64_t)blockIdx.x * ny + ty; pix < pixels; pix += (int64_t)gridDim.x * ny) {
-        const int q = (int)(pix % g.q);
-        const int p = (int)((pix / g.q) % g.p);
-        const int n = (int)(pix / ((int64_t)g.q * g.p));
-        float d[8];
-        unpack8(ld8(dy + (size_t)pix * g.c + cv * 8), d);
+    for (int k = 0; k < 8; ++k) acc[s][k] = 0.0f;
+  if (active) {
+    for (int64_t pix = (int64_t)blockIdx.x * ny + ty; pix < pixels; pix += (int64_t)gridDim.x * ny) {
+      const int q = (int)(pix % g.q);
+      const int p = (int)((pix / g.q) % g.p);
+      const int n = (int)(pix / ((int64_t)g.q * g.p));
+      const int ih = p * g.sh - g.pt + r;
+      if (ih < 0 || ih >= g.h) continue;
+      const uint4 d = __ldg(reinterpret_cast<const uint4*>(dy + (size_t)pix * g.c + cv * 8));
+      const b200_bf16* xr = x + ((size_t)(n * g.h + ih) * g.w) * g.c + cv * 8;
 #pragma unroll
-        for (int t = 0; t < kMaxTaps; ++t) {
-          if (t >= taps) break;
-          const int r = t / g.s, s = t - r * g.s;
-          const int ih = p * g.sh - g.pt + r, iw = q * g.sw - g.pl + s;
-          if (ih < 0 || ih >= g.h || iw < 0 || iw >= g.w) continue;
-          float f[8];
-          unpack8(ld8(x + (((size_t)n * g.h + ih) * g.w + iw) * g.c + cv * 8), f);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[t][k] = fmaf(f[k], d[k], acc[t][k]);
-        }
+      for (int s = 0; s < kMaxS; ++s) {
+        const int iw = q * g.sw - g.pl + s;
+        if (s < g.s && iw >= 0 && iw < g.w) fma_vec8(acc[s], __ldg(reinterpret_cast<const uint4*>(xr + (size_t)iw * g.c)), d);
       }
     }
+  }
 #pragma unroll
-    for (int t = 0; t < kMaxTaps; ++t) {
-      if (t >= taps) break;
-      __syncthreads();
+  for (int s = 0; s < kMaxS; ++s) {
+    if (s >= g.s) break;
+    __syncthreads();
 #pragma unroll
-      for (int k = 0; k < 8; ++k) red[(ty * nx + tx) * 8 + k] = acc[t][k];
-      __syncthreads();
-      if (active)
-        for (int k = ty; k < 8; k += ny) {
-          float sum = 0.0f;
-          for (int j = 0; j < ny; ++j) sum += red[(j * nx + tx) * 8 + k];
-          partials[((size_t)blockIdx.x * taps + t) * g.c + cv * 8 + k] = sum;
-        }
-    }
+    for (int k = 0; k < 8; ++k) red[(ty * nx + tx) * 8 + k] = acc[s][k];
+    __syncthreads();
+    if (active)
+      for (int k = ty; k < 8; k += ny) {
+        float sum = 0.0f;
+        for (int j = 0; j < ny; ++j) sum += red[(j * nx + tx) * 8 + k];
+        partials[((size_t)blockIdx.x * taps + r * g.s + s) * g.c + cv * 8 + k] = sum;
+      }
   }
 }
 
@@ -177,21 +207,6 @@ __global__ void __launch_bounds__(256) dw_fold_kernel(const float* __restrict__ 
 // V = 4 halves the registers per thread (twice the resident warps to hide the load latency); see dw_vec().
 
 constexpr int kT = 4;
-
-// acc += a.half[ha] * b.half[hb]: mixed-precision FMA with the bf16 operands taken in place from the packed registers
-// (PTX fma.rn.f32.bf16 = SASS FHFMA.BF16 with .H0/.H1 operand selectors on sm_100a) - exact product, one rounding, so
-// it equals an fp32 FMA of the converted values without spending instructions on the conversions. ha / hb are
-// compile-time constants at every call (fully unrolled loops), so one of the four forms survives.
-__device__ __forceinline__ void fma_bf16(float& acc, uint32_t a, int ha, uint32_t b, int hb) {
-  if (ha == 0 && hb == 0)
-    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, al, bl, %0; }" : "+f"(acc) : "r"(a), "r"(b));
-  else if (ha == 0)
-    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, al, bh, %0; }" : "+f"(acc) : "r"(a), "r"(b));
-  else if (hb == 0)
-    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, ah, bl, %0; }" : "+f"(acc) : "r"(a), "r"(b));
-  else
-    asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.bf16 %0, ah, bh, %0; }" : "+f"(acc) : "r"(a), "r"(b));
-}
 
 template <int V>
 struct Vec {                       // V bf16 values
@@ -474,6 +489,20 @@ DwLaunch dw_launch(int c, int64_t pixels, int blocks_per_sm, int vec = 8) {
   return {dim3(tx, ty), (int)(want < cap ? want : cap)};
 }
 
+// generic kernels: block = (up to 32 channel vectors, pixels), grid = (pixel blocks, channel chunks [x filter rows])
+struct GenLaunch {
+  dim3 block, grid;
+};
+GenLaunch gen_launch(int c, int64_t pixels, int blocks_per_sm, int y_mult = 1) {
+  const int cvecs = c / 8;
+  const int tx = cvecs < kGenCvecs ? cvecs : kGenCvecs, ty = 256 / tx;
+  const int gy = (cvecs + kGenCvecs - 1) / kGenCvecs * y_mult;
+  int64_t want = (pixels + ty - 1) / ty;
+  int64_t cap = (int64_t)kNumSMs * blocks_per_sm / gy;
+  if (cap < 1) cap = 1;
+  return {dim3(tx, ty), dim3((unsigned)(want < cap ? want : cap), gy)};
+}
+
 // grid stride (in runs) as (images, rows, chunks)
 RunStep run_step(const DwLaunch& l, int chunks, int rows) {
   const int stride = l.grid * (int)l.block.y;
@@ -483,7 +512,7 @@ RunStep run_step(const DwLaunch& l, int chunks, int rows) {
 int check(const b200_conv_geom* g, const char* what) {
   B200_CHECK_ARG(g, "%s: null geometry", what);
   B200_CHECK_ARG(g->k == g->c && g->c % 8 == 0, "%s: depthwise needs k == c and c %% 8 == 0 (k=%d c=%d)", what, g->k, g->c);
-  B200_CHECK_ARG(g->r * g->s <= kMaxTaps && g->r > 0 && g->s > 0, "%s: filter %dx%d has more than %d taps", what, g->r, g->s, kMaxTaps);
+  B200_CHECK_ARG(g->r > 0 && g->s > 0 && g->r <= kMaxS && g->s <= kMaxS, "%s: filter %dx%d is larger than %dx%d", what, g->r, g->s, kMaxS, kMaxS);
   B200_CHECK_ARG(g->stride_h > 0 && g->stride_w > 0 && g->n > 0 && g->p > 0 && g->q > 0, "%s: bad geometry", what);
   return 0;
 }
@@ -512,7 +541,7 @@ using namespace b200;
 extern "C" {
 
 int b200_dwconv_supported(const b200_conv_geom* g) {
-  return g && g->k == g->c && g->c % 8 == 0 && g->r > 0 && g->s > 0 && g->r * g->s <= kMaxTaps;
+  return g && g->k == g->c && g->c % 8 == 0 && g->r > 0 && g->s > 0 && g->r <= kMaxS && g->s <= kMaxS;
 }
 
 int b200_dwconv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, void* stream) {
@@ -524,7 +553,7 @@ int b200_dwconv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, cons
     DwLaunch l = dw_launch(g->c, runs, 8, dw_vec(kOpFwd));
     DW3_LAUNCH(dw3_fwd_kernel, dw_vec(kOpFwd), g->stride_h, l, st, x, w, y, to_dw(g), chunks, run_step(l, chunks, g->p));
   } else {
-    DwLaunch l = dw_launch(g->c, (int64_t)g->n * g->p * g->q, 8);
+    GenLaunch l = gen_launch(g->c, (int64_t)g->n * g->p * g->q, 8);
     dw_fwd_kernel<<<l.grid, l.block, 0, st>>>(x, w, y, to_dw(g));
   }
   B200_LAUNCH_CHECK();
@@ -542,39 +571,46 @@ int b200_dwconv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, co
     DwLaunch l = dw_launch(g->c, runs, 8, dw_vec(kOpDgrad));
     DW3_LAUNCH(dw3_dgrad_kernel, dw_vec(kOpDgrad), sw, l, st, dy, w, dx, to_dw(g), cpp, run_step(l, cpp * sw, g->h));
   } else {
-    DwLaunch l = dw_launch(g->c, (int64_t)g->n * g->h * g->w, 8);
+    GenLaunch l = gen_launch(g->c, (int64_t)g->n * g->h * g->w, 8);
     dw_dgrad_kernel<<<l.grid, l.block, 0, st>>>(dy, w, dx, to_dw(g));
   }
   B200_LAUNCH_CHECK();
   return 0;
 }
 
-static DwLaunch dw_wgrad_launch(const b200_conv_geom* g) {
-  if (fast3(g)) return dw_launch(g->c, (int64_t)g->n * g->p * ((g->q + kT - 1) / kT), dw_vec(kOpWgrad) == 4 ? 4 : 2, dw_vec(kOpWgrad));
-  return dw_launch(g->c, (int64_t)g->n * g->p * g->q, 2);
+static DwLaunch dw3_wgrad_launch(const b200_conv_geom* g) {
+  return dw_launch(g->c, (int64_t)g->n * g->p * ((g->q + kT - 1) / kT), dw_vec(kOpWgrad) == 4 ? 4 : 2, dw_vec(kOpWgrad));
+}
+static GenLaunch gen_wgrad_launch(const b200_conv_geom* g) {
+  return gen_launch(g->c, (int64_t)g->n * g->p * g->q, 4, g->r);
 }
 
 int64_t b200_dwconv_wgrad_workspace_bytes(const b200_conv_geom* g) {
   if (!b200_dwconv_supported(g)) return 0;
-  return (int64_t)dw_wgrad_launch(g).grid * g->r * g->s * g->c * (int64_t)sizeof(float);
+  const int64_t rows = fast3(g) ? dw3_wgrad_launch(g).grid : gen_wgrad_launch(g).grid.x;
+  return rows * g->r * g->s * g->c * (int64_t)sizeof(float);
 }
 
 int b200_dwconv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b200_conv_geom* g, void* workspace,
                       void* stream) {
   B200_CHECK_ARG(x && dy && dw && workspace, "dwconv_wgrad: null pointer");
   if (int e = check(g, "dwconv_wgrad")) return e;
-  DwLaunch l = dw_wgrad_launch(g);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* part = static_cast<float*>(workspace);
+  int rows;
   if (fast3(g)) {
+    DwLaunch l = dw3_wgrad_launch(g);
     const int chunks = (g->q + kT - 1) / kT;
     DW3_LAUNCH(dw3_wgrad_kernel, dw_vec(kOpWgrad), g->stride_h, l, st, x, dy, part, to_dw(g), chunks, run_step(l, chunks, g->p));
+    rows = l.grid;
   } else {
+    GenLaunch l = gen_wgrad_launch(g);
     dw_wgrad_kernel<<<l.grid, l.block, 0, st>>>(x, dy, part, to_dw(g));
+    rows = (int)l.grid.x;
   }
   B200_LAUNCH_CHECK();
   const int taps = g->r * g->s;
-  dw_fold_kernel<<<(taps * g->c + 31) / 32, dim3(32, 8), 0, st>>>(part, dw, l.grid, taps, g->c);
+  dw_fold_kernel<<<(taps * g->c + 31) / 32, dim3(32, 8), 0, st>>>(part, dw, rows, taps, g->c);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -3,7 +3,7 @@
 from __future__ import annotations
 
 from .builder import BuildConfig, Model
-from . import mobilenet, resnet, zoo, zoo2
+from . import mobilenet, nasnet, resnet, zoo, zoo2
 
 _REGISTRY = {
     "resnet50": resnet.resnet50,
@@ -21,6 +21,8 @@ _REGISTRY = {
     "overfeat": zoo.Overfeat,
     "inception4": zoo2.InceptionV4,
     "mobilenet": mobilenet.MobileNetV2,
+    "nasnet": nasnet.nasnet_mobile,
+    "nasnetlarge": nasnet.nasnet_large,
     "mobilenet_v2": lambda cfg: mobilenet.MobileNetV2(cfg, "mobilenet_v2"),
     "resnet50_v2": lambda cfg: zoo2.ResNetV2(cfg, (3, 4, 6, 3), "resnet50_v2"),
     "resnet101_v2": lambda cfg: zoo2.ResNetV2(cfg, (3, 4, 23, 3), "resnet101_v2"),

@@ -135,6 +135,13 @@ def add_relu(a, b, cfg):
     return F.relu(a + b, inplace=True)
 
 
+def relu(x, cfg):
+    """Out-of-place ReLU (the input usually feeds other branches as well)."""
+    if cfg.kernels == "b200" and x.dim() == 4 and _vec8(x.shape[1]):
+        return _b200().relu(x)
+    return F.relu(x)
+
+
 def add(a, b, cfg):
     """Residual sum without activation (pre-activation ResNets)."""
     if cfg.kernels == "b200":

@@ -504,6 +504,33 @@ class _AddAct(torch.autograd.Function):
         return dx, dx, None
 
 
+class _Relu(torch.autograd.Function):
+    """Standalone ReLU (the pre-activation in front of NASNet's separable convolutions, whose input also feeds other
+    branches un-activated): bias_act_kernel without a bias forward, relu_bwd_kernel backward (gate from the output)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = nhwc(x)
+        n, c, h, w = x.shape
+        z = empty_nhwc(n, c, h, w, x.device)
+        _check(lib().b200_bias_act(_ptr(x), _ptr(None), _ptr(z), n * h * w, c, 1, _stream()), "bias_act")
+        ctx.save_for_backward(z)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        (z,) = ctx.saved_tensors
+        dz = nhwc(dz)
+        n, c, h, w = dz.shape
+        dx = empty_nhwc(n, c, h, w, dz.device)
+        _check(lib().b200_relu_bwd(_ptr(dz), _ptr(z), _ptr(dx), dz.numel(), _stream()), "relu_bwd")
+        return dx
+
+
+def relu(x):
+    return _Relu.apply(x)
+
+
 def add_act(a, b, relu):
     if a.dim() != 4 or a.shape != b.shape or a.numel() % 8 or a.shape[1] % 8:
         return torch.relu_(a + b) if relu else a + b          # shapes the 8-channel vectors do not cover

@@ -64,9 +64,11 @@ int b200_conv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const b2
                     void* stream);
 int64_t b200_conv_wgrad_workspace_bytes(const b200_conv_geom* g);
 
-/* Depthwise convolution (groups == channels; g->k == g->c, c % 8 == 0, at most 9 filter taps; filters [C][R][S] = the
- * KRSC layout of a [C,1,R,S] weight, filter gradient fp32 in the same layout). Bandwidth-bound vector kernels
- * (csrc/kernels/depthwise.cu): MobileNet's 3x3 depthwise layers. wgrad folds its per-CTA partials in a fixed order. */
+/* Depthwise convolution (groups == channels; g->k == g->c, c % 8 == 0, filters up to 7x7, any stride; filters [C][R][S]
+ * = the KRSC layout of a [C,1,R,S] weight, filter gradient fp32 in the same layout). Bandwidth-bound vector kernels
+ * (csrc/kernels/depthwise.cu) on the mixed-precision FMA (bf16 x bf16 + fp32): a register-blocked fast path for 3x3 at
+ * stride 1 / 2 (MobileNet), shared-memory-staged taps for everything else (NASNet's 5x5 / 7x7). wgrad folds its per-CTA
+ * partials in a fixed order (bitwise reproducible). */
 int b200_dwconv_supported(const b200_conv_geom* g);
 int b200_dwconv_fprop(const b200_bf16* x, const b200_bf16* w, b200_bf16* y, const b200_conv_geom* g, void* stream);
 int b200_dwconv_dgrad(const b200_bf16* dy, const b200_bf16* w, b200_bf16* dx, const b200_conv_geom* g, void* stream);

@@ -41,6 +41,13 @@ CASES = [
     (2, 9, 13, 1040, 3, 1, ((1, 1), (1, 1))),       # more than 128 channel vectors: the per-thread channel loop
     (2, 15, 11, 40, 3, 2, ((1, 1), (1, 1))),
     (2, 10, 10, 64, 2, 2, ((0, 0), (0, 0))),
+    # generic kernels (taps staged in shared memory): NASNet's 5x5 / 7x7 separable convolutions, a 3x3 at stride 3
+    (2, 28, 28, 88, 5, 1, ((2, 2), (2, 2))),
+    (2, 28, 28, 88, 7, 2, ((2, 3), (2, 3))),
+    (3, 14, 14, 176, 7, 1, ((3, 3), (3, 3))),
+    (2, 9, 9, 352, 5, 2, ((2, 2), (2, 2))),
+    (2, 11, 7, 1040, 5, 1, ((2, 2), (2, 2))),       # five channel chunks of 32 vectors
+    (2, 13, 13, 48, 3, 3, ((1, 1), (1, 1))),
 ]
 
 
@@ -121,3 +128,13 @@ def test_mobilenet_trains_on_own_kernels_and_loss_falls():
     paths = dict(conv_impl.path_counts)
     assert paths.get("fprop_depthwise") == 17 * 12 and paths.get("dgrad_depthwise") == 17 * 12 and paths.get("wgrad_depthwise") == 17 * 12, paths
     assert not {k: n for k, n in paths.items() if k.endswith("_lib") and not k.startswith("gemm")}, paths
+
+
+def test_standalone_relu_node():
+    from azure_hc_intel_tf_b200.ops import b200
+    x = rnd(3, 9, 11, 40, 11).requires_grad_(True)
+    z = b200.relu(x)
+    dz = rnd(3, 9, 11, 40, 12)
+    z.backward(dz)
+    assert torch.equal(z, torch.relu(x.detach())) and z.data_ptr() != x.data_ptr()
+    assert torch.equal(x.grad, torch.where(x.detach() > 0, dz, torch.zeros_like(dz)))

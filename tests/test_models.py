@@ -13,6 +13,9 @@ EXPECTED_PARAMS = {          # trainable parameters with 1001 classes
     "resnet50": 25559081, "resnet101": 44551209, "resnet152": 60194857, "vgg16": 138361641, "vgg19": 143671337,
     "inception3": 23819401, "googlenet": 6999577, "alexnet": 61842345,
     "resnet50_v2": 25551529, "inception4": 42649769, "mobilenet": 3506153,
+    # NASNet-A: the published Keras / slim sizes are 5,289,978 (mobile) and 88,753,150 (large) trainable parameters
+    # with 1000 classes; the 1001st class adds 1056 + 1 and 4032 + 1
+    "nasnet": 5289978 + 1057, "nasnetlarge": 88753150 + 4033,
     # CIFAR-10 models (11 classes): the published sizes are 0.27 M / 0.85 M / 1.7 M (ResNet-20/56/110) and
     # 1.0 M / 7.0 M / 27.2 M (DenseNet 40-k12 / 100-k12 / 100-k24)
     "resnet20": 269787, "resnet56": 853083, "resnet110": 1728027, "resnet20_v2": 269787,
@@ -34,7 +37,7 @@ def test_resnet50_has_161_trainable_tensors_and_53_convs():
 
 
 @pytest.mark.parametrize("name", ["resnet50", "googlenet", "lenet", "trivial", "resnet50_v2", "resnet20", "resnet32_v2",
-                                  "densenet40_k12", "inception4", "mobilenet"])
+                                  "densenet40_k12", "inception4", "mobilenet", "nasnet"])
 def test_forward_backward_shapes(name):
     m = create_model(name)
     x = torch.randn(2, 3, m.image_size, m.image_size).contiguous(memory_format=torch.channels_last)
@@ -110,3 +113,18 @@ def test_relu6_and_grouped_conv_on_the_stock_path_match_torch():
     c.activation = None
     assert torch.allclose(c(x, residual=r), F.batch_norm(F.conv2d(F.pad(x, (pl, pr, pt, pb)), c.weight, None, 2, 0, 1, 16),
                                                          None, None, c.bn.gamma, c.bn.beta, True, 0.0, c.bn.eps) + r, atol=1e-5)
+
+
+def test_nasnet_cell_structure():
+    """16 cells for the mobile model (2 stem reductions, 3 x 4 normal, 2 reductions), channel widths 6F / 4F, separable
+    convolutions with 3x3 / 5x5 / 7x7 depthwise halves; the large model keeps p across a reduction cell."""
+    from azure_hc_intel_tf_b200.models.builder import Conv
+    m = create_model("nasnet")
+    assert [c.reduction for c in m.cells] == [True, True] + [False] * 4 + [True] + [False] * 4 + [True] + [False] * 4
+    assert [c.out[0] for c in m.cells] == [44, 88] + [264] * 4 + [352] + [528] * 4 + [704] + [1056] * 4
+    assert m.cells[-1].out[1] == (7, 7) and not any(c.keep_p for c in m.cells)
+    assert m.cells[0].adjust.mode == "same" and m.cells[1].adjust.mode == "reduce" and m.cells[3].adjust.mode == "project"
+    ks = {c.k for c in m.modules() if isinstance(c, Conv) and c.groups > 1}
+    assert ks == {(3, 3), (5, 5), (7, 7)}
+    big = create_model("nasnetlarge")
+    assert len(big.cells) == 2 + 3 * 6 + 2 and sum(c.keep_p for c in big.cells) == 2 and big.image_size == 331
