@@ -138,3 +138,44 @@ def test_standalone_relu_node():
     z.backward(dz)
     assert torch.equal(z, torch.relu(x.detach())) and z.data_ptr() != x.data_ptr()
     assert torch.equal(x.grad, torch.where(x.detach() > 0, dz, torch.zeros_like(dz)))
+
+
+@pytest.mark.parametrize("c,k,stride", [(40, 3, 1), (96, 3, 2), (88, 5, 2), (1040, 7, 1)])
+def test_depthwise_kernels_stay_inside_their_buffers(c, k, stride):
+    """Guard bands (compute-sanitizer is closed on this pool): every output and the wgrad workspace sit between two
+    sentinel regions that must come back untouched, on odd sizes that leave partial chunks at the row ends."""
+    import ctypes as C
+    from azure_hc_intel_tf_b200.ops import conv_umma
+    from azure_hc_intel_tf_b200.ops.b200 import _check, _ptr, _stream, lib
+    n, h, w = 2, 13, 11
+    pad = ((k // 2, k // 2), (k // 2, k // 2))
+    m = M(c, k, stride, pad, (h, w))
+    g = conv_umma.geom((n, c, h, w), m)
+    p, q = m.out_hw
+    x = rnd(n, h, w, c, 21).contiguous(memory_format=torch.channels_last)
+    dy = rnd(n, p, q, c, 22).contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(c, 1, k, k) / k).to(DEV).to(torch.bfloat16)
+    guard = 4096
+
+    def banded(numel, dtype, fill):
+        buf = torch.full((numel + 2 * guard,), fill, dtype=dtype, device=DEV)
+        return buf, buf[guard:guard + numel]
+
+    def intact(buf, numel, fill):
+        return bool((buf[:guard] == fill).all()) and bool((buf[guard + numel:] == fill).all())
+
+    ybuf, y = banded(n * p * q * c, torch.bfloat16, 7.0)
+    _check(lib().b200_dwconv_fprop(_ptr(x), _ptr(wt), _ptr(y), C.byref(g), _stream()), "dwconv_fprop")
+    dxbuf, dx = banded(n * h * w * c, torch.bfloat16, 7.0)
+    _check(lib().b200_dwconv_dgrad(_ptr(dy), _ptr(wt), _ptr(dx), C.byref(g), _stream()), "dwconv_dgrad")
+    ws_bytes = lib().b200_dwconv_wgrad_workspace_bytes(C.byref(g))
+    wsbuf, ws = banded(ws_bytes // 4, torch.float32, 7.0)
+    dwbuf, dw = banded(c * k * k, torch.float32, 7.0)
+    _check(lib().b200_dwconv_wgrad(_ptr(x), _ptr(dy), _ptr(dw), C.byref(g), _ptr(ws), _stream()), "dwconv_wgrad")
+    torch.cuda.synchronize()
+    assert intact(ybuf, y.numel(), 7.0) and intact(dxbuf, dx.numel(), 7.0)
+    assert intact(wsbuf, ws.numel(), 7.0) and intact(dwbuf, dw.numel(), 7.0)
+    # and the results are the same as through the allocating wrappers
+    assert torch.equal(y.view(n, p, q, c).permute(0, 3, 1, 2), conv_umma.dw_fprop(x, wt, m))
+    assert torch.equal(dx.view(n, h, w, c).permute(0, 3, 1, 2), conv_umma.dw_dgrad(dy, wt, m, x.shape))
+    assert torch.equal(dw.view(c, 1, k, k), conv_umma.dw_wgrad(x, dy, m).reshape(c, 1, k, k))
