@@ -1190,18 +1190,21 @@ int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n) { return grid_for
 int b200_gemm_nt_stats(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k,
                        int32_t ldo, int32_t out_fp32, float* col_stats, void* stream) {
   B200_CHECK_ARG(a && b && out, "gemm_nt: null pointer");
-  B200_CHECK_ARG(m > 0 && n > 0 && k > 0 && k % 64 == 0 && ldo >= n, "gemm_nt: need k%%64==0 and ldo>=n");
+  // k need not be a multiple of the 64-wide k-block: the last block's columns past k are zero-filled by TMA in both
+  // operands (rows must stay 16-byte aligned, hence k % 8)
+  B200_CHECK_ARG(m > 0 && n > 0 && k > 0 && k % 8 == 0 && ldo >= n, "gemm_nt: need k%%8==0 and ldo>=n");
   CUtensorMap ma, mb;
   GemmParams p{};
   p.M = m;
   p.N = n;
   p.block_n = pick_block_n(n);
   p.num_m_tiles = (m + kBlockM - 1) / kBlockM;
-  p.ctas = col_stats ? 1 : plan_ctas(p.block_n, p.num_m_tiles, k / kBlockK, false);
+  const int kblocks = (k + kBlockK - 1) / kBlockK;
+  p.ctas = col_stats ? 1 : plan_ctas(p.block_n, p.num_m_tiles, kblocks, false);
   if (tmap_tiled_2d(&ma, a, 2, (uint64_t)k, (uint64_t)m, (uint64_t)k * 2, kBlockK, kBlockM, true)) return -1;
   if (tmap_tiled_2d(&mb, b, 2, (uint64_t)k, (uint64_t)n, (uint64_t)k * 2, kBlockK, p.block_n / p.ctas, true)) return -1;
   p.num_n_tiles = (n + p.block_n - 1) / p.block_n;
-  p.cchunks = k / kBlockK;
+  p.cchunks = kblocks;
   p.num_k_blocks = p.cchunks;
   p.R = p.S = 1;
   p.out = out;

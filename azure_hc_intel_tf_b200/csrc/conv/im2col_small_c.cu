@@ -90,7 +90,7 @@ extern "C" int b200_im2col_small_c(const b200_bf16* x, b200_bf16* a, const b200_
   using namespace b200;
   B200_CHECK_ARG(x && a && g, "im2col_small_c: null pointer");
   const int kdim = g->r * g->s * g->c;
-  B200_CHECK_ARG(kpad >= kdim && kpad % 64 == 0, "im2col_small_c: kpad must be a multiple of 64 and >= R*S*C");
+  B200_CHECK_ARG(kpad >= kdim && kpad % 8 == 0, "im2col_small_c: kpad must be a multiple of 8 and >= R*S*C");
   // pixels per strip: a whole output row when its staged window fits, else the largest strip that does
   const int kvecs = kpad / 8;
   int qt = g->q;

@@ -46,7 +46,7 @@ def supports_wgrad(x, dy, m) -> bool:
 
 
 def supports_gemm(m_, n_, k_) -> bool:
-    return "gemm" not in _disabled and k_ % 64 == 0
+    return "gemm" not in _disabled and k_ % 8 == 0
 
 
 def fprop(x, w_lp, m, want_stats: bool = False):
@@ -178,7 +178,11 @@ def supports_first_layer(x, m) -> bool:
 
 
 def first_layer_kpad(m) -> int:
-    return (m.k[0] * m.k[1] * m.cin + 63) // 64 * 64
+    """Row length of the patch matrix: R*S*Cin rounded up to the 8-element (16-byte) rows TMA needs - 152 for the 7x7x3
+    ImageNet stem; the GEMM's last 64-wide k-block is zero-filled by TMA past it. B200_FIRST_KPAD=64 restores rounding
+    to whole k-blocks (192: 26 % more patch-matrix bytes written once and read twice per step)."""
+    unit = 64 if os.environ.get("B200_FIRST_KPAD") == "64" else 8
+    return (m.k[0] * m.k[1] * m.cin + unit - 1) // unit * unit
 
 
 def first_layer_fprop(x, w_lp, m, want_stats: bool):

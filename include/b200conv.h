@@ -76,7 +76,8 @@ int b200_dwconv_wgrad(const b200_bf16* x, const b200_bf16* dy, float* dw, const 
                       void* stream);
 int64_t b200_dwconv_wgrad_workspace_bytes(const b200_conv_geom* g);
 
-/* out[m, n] = a[m, k] . b[n, k]^T ; a, b row-major bf16, k % 64 == 0; out bf16 or fp32 with leading dimension ldo. */
+/* out[m, n] = a[m, k] . b[n, k]^T ; a, b row-major bf16, k % 8 == 0 (a partial last 64-wide k-block is zero-filled by
+ * TMA); out bf16 or fp32 with leading dimension ldo. */
 int b200_gemm_nt(const b200_bf16* a, const b200_bf16* b, void* out, int32_t m, int32_t n, int32_t k, int32_t ldo,
                  int32_t out_fp32, void* stream);
 
@@ -88,7 +89,7 @@ int64_t b200_gemm_stats_rows(int32_t m, int32_t n);
 int64_t b200_gemm_stats_first_result_row(int32_t m, int32_t n);
 
 /* Patch matrix for small-Cin (first-layer) convolutions: a[n*p*q][kpad] bf16, column (r*S + s)*Cin + c, zero padded
- * from R*S*Cin up to kpad (a multiple of 64). Forward: gemm_nt(a, w_padded); weight gradient: dense_wgrad(a, dy). */
+ * from R*S*Cin up to kpad (a multiple of 8). Forward: gemm_nt(a, w_padded); weight gradient: dense_wgrad(a, dy). */
 int b200_im2col_small_c(const b200_bf16* x, b200_bf16* a, const b200_conv_geom* g, int32_t kpad, void* stream);
 
 /* out[m, n] (bf16) = a[m, k] . b[k, n]; a has leading dimension lda >= k (multiple of 8; elements past k must be

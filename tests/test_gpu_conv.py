@@ -116,7 +116,8 @@ def test_dgrad(n, h, w, cin, cout, k, stride, pad):
     assert rel_err(dx, xf.grad) < 1e-2
 
 
-@pytest.mark.parametrize("mm,nn,kk", [(256, 1001, 2048), (64, 4096, 25088), (256, 4096, 4096), (100, 16, 64)])
+@pytest.mark.parametrize("mm,nn,kk", [(256, 1001, 2048), (64, 4096, 25088), (256, 4096, 4096), (100, 16, 64),
+                                      (300, 64, 152), (64, 1001, 1056), (130, 72, 8)])   # partial last k-block
 def test_gemm_nt(mm, nn, kk):
     from azure_hc_intel_tf_b200.ops import conv_umma
     g = torch.Generator().manual_seed(0)
