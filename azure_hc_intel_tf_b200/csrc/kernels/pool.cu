@@ -79,32 +79,31 @@ __global__ void __launch_bounds__(256) maxpool_fwd_fixed_kernel(const b200_bf16*
       for (int s = 0; s < KW; ++s) {
         const int h = h0 + r, w = w0 + s;
         ok[r * KW + s] = h >= 0 && h < g.h && w >= 0 && w < g.w;
-        if (ok[r * KW + s]) v[r * KW + s] = ld8(x + (((int64_t)n * g.h + h) * g.w + w) * g.c + c8 * 8);
+        if (ok[r * KW + s]) v[r * KW + s] = ld8(x + (((n * g.h + h) * g.w + w) * g.c + c8 * 8));   // 32-bit offsets (host-checked)
       }
-    float best[8];
-    int arg[8];
+    // running maximum and its tap index, both kept packed (two bf16 / two 16-bit indices per register): one packed
+    // compare and two bit-selects per channel pair and tap, no conversions. Strict '>' keeps the first maximum.
+    uint32_t best[4], arg[4];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      best[k] = -INFINITY;
-      arg[k] = 0;
+    for (int k = 0; k < 4; ++k) {
+      best[k] = 0xff80ff80u;      // (-inf, -inf)
+      arg[k] = 0u;
     }
 #pragma unroll
     for (int j = 0; j < KH * KW; ++j) {
       if (!ok[j]) continue;
-      float f[8];
-      unpack8(v[j], f);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (f[k] > best[k]) {
-          best[k] = f[k];
-          arg[k] = j;
-        }
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t xv = *reinterpret_cast<const uint32_t*>(&v[j].v[k]);
+        const uint32_t gt = __hgt2_mask(v[j].v[k], *reinterpret_cast<const __nv_bfloat162*>(&best[k]));   // 0xffff per lane
+        best[k] = (xv & gt) | (best[k] & ~gt);
+        arg[k] = ((uint32_t)j * 0x00010001u & gt) | (arg[k] & ~gt);
       }
     }
-    st8(y + (int64_t)i * 8, pack8(best));
-    uint2 pk;
-    pk.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
-    pk.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    *reinterpret_cast<uint4*>(y + (int64_t)i * 8) = make_uint4(best[0], best[1], best[2], best[3]);
+    uint2 pk;                                          // index bytes 0 and 2 of each register pair
+    pk.x = __byte_perm(arg[0], arg[1], 0x6420);
+    pk.y = __byte_perm(arg[2], arg[3], 0x6420);
     *reinterpret_cast<uint2*>(idx + (int64_t)i * 8) = pk;
   }
 }
@@ -174,7 +173,6 @@ __global__ void __launch_bounds__(256) maxpool_bwd_block_kernel(const b200_bf16*
     const int bh = (int)(t % hb);
     const int n = (int)(t / hb);
     const int h0 = bh * SH, w0 = bw * SW;
-    const int kw_recip = (65536 + g.kw - 1) / g.kw;
     float acc[SH][SW][8];
 #pragma unroll
     for (int a = 0; a < SH; ++a)
@@ -199,16 +197,24 @@ __global__ void __launch_bounds__(256) maxpool_bwd_block_kernel(const b200_bf16*
         const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
         float f[8];
         unpack8(ld8(dy + o), f);
+        // the tap of this output's window that lands on each pixel of the block (thread-uniform scalars; 255 = none),
+        // so that per channel only byte compares and predicated adds remain
+        int tgt[SH][SW];
+#pragma unroll
+        for (int aa = 0; aa < SH; ++aa)
+#pragma unroll
+          for (int bb = 0; bb < SW; ++bb) {
+            const int r = aa - dh0, s2 = bb - dw0;
+            tgt[aa][bb] = (r >= 0 && r < g.kh && s2 >= 0 && s2 < g.kw) ? r * g.kw + s2 : 255;
+          }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const int a = ((k < 4 ? pk.x : pk.y) >> (8 * (k & 3))) & 0xff;
-          const int r = (a * kw_recip) >> 16, s2 = a - r * g.kw;     // a / kw, exact for a < 256
-          const int dh = dh0 + r, dw = dw0 + s2;
 #pragma unroll
           for (int aa = 0; aa < SH; ++aa)
 #pragma unroll
             for (int bb = 0; bb < SW; ++bb)
-              if (dh == aa && dw == bb) acc[aa][bb][k] += f[k];
+              if (a == tgt[aa][bb]) acc[aa][bb][k] += f[k];
         }
       }
     }
@@ -374,12 +380,13 @@ int b200_maxpool_fwd(const b200_bf16* x, b200_bf16* y, uint8_t* idx, const b200_
   B200_CHECK_ARG(x && y && idx, "maxpool_fwd: null pointer");
   int64_t total = (int64_t)g->n * g->p * g->q * (g->c / 8);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (total < (1ll << 31) && g->kh == 3 && g->kw == 3) {
+  const bool small = total < (1ll << 31) && (int64_t)g->n * g->h * g->w * g->c < (1ll << 31);   // 32-bit element offsets
+  if (small && g->kh == 3 && g->kw == 3) {
     maxpool_fwd_fixed_kernel<3, 3><<<grid_for(total, 256), 256, 0, st>>>(x, y, idx, *g);
     B200_LAUNCH_CHECK();
     return 0;
   }
-  if (total < (1ll << 31) && g->kh == 2 && g->kw == 2) {
+  if (small && g->kh == 2 && g->kw == 2) {
     maxpool_fwd_fixed_kernel<2, 2><<<grid_for(total, 256), 256, 0, st>>>(x, y, idx, *g);
     B200_LAUNCH_CHECK();
     return 0;
