@@ -11,12 +11,23 @@
 // divides 256), so scale/shift and the backward coefficients are loaded once per thread, not once per element.
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace b200 {
 namespace {
 
 constexpr int kThreads = 256;
 constexpr int kTargetBlocks = 8 * kNumSMs;   // elementwise passes: ~8 CTAs per SM
-constexpr int kReduceBlocks = 3 * kNumSMs;   // column reductions: one wave of 3 CTAs per SM keeps the final fold short
+// Column reductions run as one wave of kOcc CTAs per SM (a short final fold). kOcc = 2 lets a thread keep 128 registers,
+// enough for all sixteen 16-byte loads of an eight-row trip to be in flight at once; with 3 CTAs per SM (85 registers)
+// the compiler has to serialise them and the kernel stalls on load latency (B200_REDUCE_OCC=3 restores that).
+inline int reduce_occ() {
+  static const int occ = [] {
+    const char* e = getenv("B200_REDUCE_OCC");
+    return (e && e[0] == '3') ? 3 : 2;
+  }();
+  return occ;
+}
 constexpr int kScratchHeader = 64;           // floats reserved in front of the partials (one ticket per channel chunk)
 
 struct ColGeom {
@@ -34,7 +45,7 @@ inline ColGeom col_geom(int64_t rows, int c) {
   g.ty = kThreads / g.tx;
   g.ychunks = (g.cvecs + g.tx - 1) / g.tx;
   int64_t b = (rows + (int64_t)g.ty * 8 - 1) / ((int64_t)g.ty * 8);
-  int cap = kReduceBlocks / g.ychunks;
+  int cap = reduce_occ() * kNumSMs / g.ychunks;
   if (cap < 1) cap = 1;
   g.blocks = (int)(b < 1 ? 1 : (b > cap ? cap : b));
   return g;
@@ -51,6 +62,7 @@ struct StatsPolicy {
   int64_t rows;
   int c;
 
+  static constexpr bool kBatched = false;
   __device__ __forceinline__ void prepare(int) {}
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float f[8];
@@ -100,28 +112,41 @@ struct BwdReducePolicy {
       }
     }
   }
-  // accumulates a = sum g and b = sum g*x; dgamma = rstd * (b - mean * a) is formed once per channel in finalize
-  __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
-    float g[8], xv[8];
+  // accumulates a = sum g and b = sum g*x; dgamma = rstd * (b - mean * a) is formed once per channel in finalize.
+  // Split into fetch (loads only, no data-dependent branch) and accum so that the skeleton can put the loads of several
+  // rows in flight before the first use: with the mode branches between the loads the compiler issued two loads per
+  // row and waited, and the kernel ran at 58 % of copy bandwidth on load latency.
+  static constexpr bool kBatched = true;
+  static constexpr int kRows = 4;
+  struct Row {
+    bf16x8 g, x;
+    unsigned m;
+    int64_t off;     // only read in the (rare) mask-from-z mode, which loads z at accumulation time
+  };
+  __device__ __forceinline__ Row fetch(int64_t row, int cv) const {
+    Row r;
     const int64_t off = row * c + cv * 8;
-    const bf16x8 gq = ld8_stream(dz + off), xq = ld8_stream(x + off);
-    if (relu && mask) {
-      const unsigned mb = __ldg(mask + (off >> 3));
-      unpack8(gq, g);
+    r.g = ld8_stream(dz + off);
+    r.x = ld8_stream(x + off);
+    r.m = 0xffu;
+    r.off = off;
+    if (relu && mask) r.m = __ldg(mask + (off >> 3));
+    return r;
+  }
+  __device__ __forceinline__ void accum(const Row& r, float a[8], float b[8]) const {
+    float g[8], xv[8];
+    unpack8(r.g, g);
+    unpack8(r.x, xv);
+    if (relu) {
+      if (mask) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) g[i] = (mb >> i) & 1u ? g[i] : 0.0f;
-      unpack8(xq, xv);
-    } else if (relu && z) {
-      float zv[8];
-      unpack8(ld8_stream(z + off), zv);
-      unpack8(gq, g);
+        for (int i = 0; i < 8; ++i) g[i] = (r.m >> i) & 1u ? g[i] : 0.0f;
+      } else if (z) {
+        float zv[8];
+        unpack8(ld8_stream(z + r.off), zv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
-      unpack8(xq, xv);
-    } else {
-      unpack8(gq, g);
-      unpack8(xq, xv);
-      if (relu) {
+        for (int i = 0; i < 8; ++i) g[i] = zv[i] > 0.0f ? g[i] : 0.0f;
+      } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) g[i] = fmaf(k_scale[i], xv[i], k_shift[i]) > 0.0f ? g[i] : 0.0f;
       }
@@ -132,6 +157,7 @@ struct BwdReducePolicy {
       b[i] = fmaf(g[i], xv[i], b[i]);
     }
   }
+  __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const { accum(fetch(row, cv), a, b); }
   __device__ __forceinline__ void finalize(int ch, float s1, float s2) const {
     dbeta[ch] = s1;
     dgamma[ch] = rstd[ch] * (s2 - mean[ch] * s1);
@@ -145,6 +171,7 @@ struct BiasBwdPolicy {
   int relu;
   int c;
 
+  static constexpr bool kBatched = false;
   __device__ __forceinline__ void prepare(int) {}
   __device__ __forceinline__ void load(int64_t row, int cv, float a[8], float b[8]) const {
     float g[8];
@@ -168,9 +195,9 @@ struct BiasBwdPolicy {
 
 // ---- skeleton -------------------------------------------------------------------------------------
 
-template <class Policy>
-__global__ void __launch_bounds__(kThreads, 3) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
-                                                                 float* scratch) {
+template <class Policy, int kOcc>
+__global__ void __launch_bounds__(kThreads, kOcc) col_reduce_kernel(Policy pol, int64_t rows, int c, ColGeom g,
+                                                                    float* scratch) {
   __shared__ float sm[kThreads * 16];
   __shared__ int is_last;
   const int tid = threadIdx.x;
@@ -184,10 +211,22 @@ __global__ void __launch_bounds__(kThreads, 3) col_reduce_kernel(Policy pol, int
     pol.prepare(cv);
     const int64_t stride = (int64_t)gridDim.x * g.ty;
     int64_t r = (int64_t)blockIdx.x * g.ty + ty;
-    // eight rows per trip: eight independent groups of 16-byte loads in flight per thread
-    for (; r + 7 * stride < rows; r += 8 * stride) {
+    if constexpr (Policy::kBatched) {
+      // kRows rows per trip, every load of the trip issued before the first use
+      constexpr int U = Policy::kRows;
+      for (; r + (U - 1) * stride < rows; r += U * stride) {
+        typename Policy::Row rw[U];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) pol.load(r + u * stride, cv, a, b);
+        for (int u = 0; u < U; ++u) rw[u] = pol.fetch(r + u * stride, cv);
+#pragma unroll
+        for (int u = 0; u < U; ++u) pol.accum(rw[u], a, b);
+      }
+    } else {
+      // eight rows per trip: eight independent groups of 16-byte loads in flight per thread
+      for (; r + 7 * stride < rows; r += 8 * stride) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) pol.load(r + u * stride, cv, a, b);
+      }
     }
     for (; r < rows; r += stride) pol.load(r, cv, a, b);
   }
@@ -270,7 +309,10 @@ int launch_col_reduce(const Policy& pol, int64_t rows, int c, void* scratch, cud
   ColGeom g = col_geom(rows, c);
   B200_CHECK_ARG(g.ychunks <= kScratchHeader, "column reduce: too many channels (c=%d)", c);
   dim3 grid(g.blocks, g.ychunks);
-  col_reduce_kernel<Policy><<<grid, kThreads, 0, st>>>(pol, rows, c, g, static_cast<float*>(scratch));
+  if (reduce_occ() == 3)
+    col_reduce_kernel<Policy, 3><<<grid, kThreads, 0, st>>>(pol, rows, c, g, static_cast<float*>(scratch));
+  else
+    col_reduce_kernel<Policy, 2><<<grid, kThreads, 0, st>>>(pol, rows, c, g, static_cast<float*>(scratch));
   B200_LAUNCH_CHECK();
   return 0;
 }
