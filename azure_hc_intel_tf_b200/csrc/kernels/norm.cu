@@ -501,17 +501,36 @@ __global__ void bn_finalize_kernel(StatsPolicy pol, const float* sums, int c) {
   if (ch < c) pol.bn_finish(ch, sums[ch], sums[c + ch]);
 }
 
-// Fold [nrows][2][c] partial sums (conv epilogue) in row order, then finalise. Block = 32 channels x 8 row slices.
-__global__ void __launch_bounds__(256) bn_finalize_partials_kernel(StatsPolicy pol, const float* __restrict__ part,
-                                                                   int64_t nrows, int c) {
-  __shared__ float sm[2][8][33];
+// Fold [nrows][2][c] partial sums (conv epilogue) in a fixed order, then finalise. Block = 32 channels x 32 row slices:
+// a slice is a handful of rows (nrows is one or two per SM), all of whose loads are issued before the first add - the
+// kernel is a chain of L2 round trips, not bandwidth, so its length is the number of dependent trips (it was twenty with
+// 8 slices and a rolled loop: 11 us per BN layer, 53 layers per step).
+constexpr int kFinSlices = 32;
+__global__ void __launch_bounds__(32 * kFinSlices) bn_finalize_partials_kernel(StatsPolicy pol, const float* __restrict__ part,
+                                                                                int64_t nrows, int c) {
+  __shared__ float sm[2][kFinSlices][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int ch = blockIdx.x * 32 + tx;
   float s1 = 0.0f, s2 = 0.0f;
   if (ch < c) {
     // contiguous row ranges per slice keep the summation order fixed
-    const int64_t lo = nrows * ty / 8, hi = nrows * (ty + 1) / 8;
-    for (int64_t r = lo; r < hi; ++r) {
+    const int64_t lo = nrows * ty / kFinSlices, hi = nrows * (ty + 1) / kFinSlices;
+    int64_t r = lo;
+    for (; r + 4 <= hi; r += 4) {
+      float v1[4], v2[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* p = part + (r + u) * 2 * c;
+        v1[u] = __ldcg(p + ch);
+        v2[u] = __ldcg(p + c + ch);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        s1 += v1[u];
+        s2 += v2[u];
+      }
+    }
+    for (; r < hi; ++r) {
       const float* p = part + r * 2 * c;
       s1 += __ldcg(p + ch);
       s2 += __ldcg(p + c + ch);
@@ -523,7 +542,7 @@ __global__ void __launch_bounds__(256) bn_finalize_partials_kernel(StatsPolicy p
   if (ty == 0 && ch < c) {
     float a = 0.0f, b = 0.0f;
 #pragma unroll
-    for (int y = 0; y < 8; ++y) {
+    for (int y = 0; y < kFinSlices; ++y) {
       a += sm[0][y][tx];
       b += sm[1][y][tx];
     }
@@ -649,7 +668,7 @@ int b200_bn_finalize_partials(const float* partials, int64_t nrows, int64_t rows
                               float* mean, float* rstd, float* scale, float* shift, void* stream) {
   B200_CHECK_ARG(partials && mean && rstd && scale && shift && nrows > 0, "bn_finalize_partials: bad args");
   StatsPolicy pol{nullptr, gamma, beta, running_mean, running_var, decay, eps, mean, rstd, scale, shift, rows, c};
-  bn_finalize_partials_kernel<<<(c + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(pol, partials, nrows, c);
+  bn_finalize_partials_kernel<<<(c + 31) / 32, 32 * kFinSlices, 0, static_cast<cudaStream_t>(stream)>>>(pol, partials, nrows, c);
   B200_LAUNCH_CHECK();
   return 0;
 }

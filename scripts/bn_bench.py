@@ -59,3 +59,18 @@ for hw, c, count in ((56, 64, 6), (56, 256, 4), (28, 128, 8), (28, 512, 5), (14,
         print(f"| {rows} x {c} | {mode} | {t:.1f} | {gbs:.0f} | {100 * gbs / HBM:.0f} |")
 for mode, (t, r) in tot.items():
     print(f"\nResNet-50 weighted sum, {mode}: {t / 1e3:.2f} ms vs roofline {r / 1e3:.2f} ms ({100 * r / t:.0f} %)")
+
+# the per-layer statistics fold (conv-epilogue partial sums -> mean / rstd / scale / shift): a latency chain, not bandwidth
+print("\n| partial rows x c | bn_finalize_partials us |\n|---|---:|")
+fin = 0.0
+for nrows, c, count in ((148, 64, 7), (148, 256, 16), (148, 128, 8), (148, 512, 11), (148, 1024, 7), (148, 2048, 4), (296, 256, 4)):
+    part = torch.randn(nrows, 2, c, device=dev).abs()
+    g_, b_ = torch.ones(c, device=dev), torch.zeros(c, device=dev)
+    rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
+    out = torch.empty(4, c, device=dev)
+    fn = lambda: _check(lib().b200_bn_finalize_partials(_ptr(part), nrows, 200704, c, _ptr(g_), _ptr(b_), _ptr(rm), _ptr(rv), 0.9, 1e-5,
+                                                        _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _ptr(out[3]), _stream()), "fin")
+    t = med(fn)
+    fin += t * count
+    print(f"| {nrows} x {c} | {t:.1f} |")
+print(f"\nResNet-50 weighted sum of the statistics folds: {fin / 1e3:.2f} ms")
