@@ -80,8 +80,8 @@ def main():
     json.dump(out, open(os.path.join(a.out, "depthwise_bench.json"), "w"), indent=1)
     with open(os.path.join(a.out, "depthwise_bench.md"), "w") as f:
         f.write(f"# Depthwise 3x3 kernels, MobileNet-v2 shapes, batch {a.batch} (µs, median of {a.iters}, L2 flushed; roofline = "
-                f"(input + output bytes) / {hbm:.0f} GB/s). The flush leaves the 126 MB L2 full of dirty lines whose write-back lands inside "
-                "the timed kernel: about 13 µs of every figure, the library's included, is that floor)\n\n"
+                f"(input + output bytes) / {hbm:.0f} GB/s). About 13 µs of every figure, the library's included, is a floor of this harness: "
+                "the host's launch latency behind the flush kernel and the write-back of the flush's dirty L2 lines)\n\n"
                 "| layer | roofline | fprop | dgrad | wgrad | cuDNN fprop | cuDNN dgrad | cuDNN wgrad |\n"
                 "|---|---:|---:|---:|---:|---:|---:|---:|\n")
         for r in rows:
