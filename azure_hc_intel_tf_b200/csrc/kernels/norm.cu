@@ -18,9 +18,9 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kTargetBlocks = 8 * kNumSMs;   // elementwise passes: ~8 CTAs per SM
-// Column reductions run as one wave of kOcc CTAs per SM (a short final fold). kOcc = 2 lets a thread keep 128 registers,
-// enough for all sixteen 16-byte loads of an eight-row trip to be in flight at once; with 3 CTAs per SM (85 registers)
-// the compiler has to serialise them and the kernel stalls on load latency (B200_REDUCE_OCC=3 restores that).
+// Column reductions run as one wave of kOcc CTAs per SM (a short final fold). kOcc = 2 lets a thread keep 128 registers:
+// the BN backward reduce holds the loads of four rows (8 vector + 4 mask loads) in flight and needs 126. With 3 CTAs per
+// SM (85 registers) that batch spills; B200_REDUCE_OCC=3 selects it anyway for A/B runs (measured slower).
 inline int reduce_occ() {
   static const int occ = [] {
     const char* e = getenv("B200_REDUCE_OCC");
