@@ -286,6 +286,29 @@ def broadcast_parameters(params, root_rank: int = 0) -> None:
                 off += n
 
 
+def broadcast_global_variables(model, root_rank: int = 0, optimizer=None) -> None:
+    """``horovod.tensorflow.broadcast_global_variables(root_rank)``: TensorFlow's "global variables" are the model's
+    parameters, its non-trainable state (BN moving statistics) and the optimizer slots; here they are named explicitly."""
+    broadcast_parameters(model.state_dict(), root_rank)
+    if optimizer is not None:
+        broadcast_optimizer_state(optimizer, root_rank)
+
+
+class BroadcastGlobalVariablesHook:
+    """``hvd.BroadcastGlobalVariablesHook(0)``, the session hook tf_cnn_benchmarks installs under
+    ``--variable_update=horovod`` (run-tf-sing-ucx-openmpi.sh:77): call ``begin(model, optimizer)`` once after the
+    variables exist and before the first step."""
+
+    def __init__(self, root_rank: int = 0):
+        self.root_rank = root_rank
+        self.done = False
+
+    def begin(self, model, optimizer=None) -> None:
+        if not self.done:
+            broadcast_global_variables(model, self.root_rank, optimizer)
+            self.done = True
+
+
 def broadcast_optimizer_state(optimizer, root_rank: int = 0) -> None:
     _need()
     if size() == 1:

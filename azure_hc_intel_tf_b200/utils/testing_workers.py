@@ -21,6 +21,15 @@ def w_basic(rank, world):
         pass
     z = hvd.synchronize(h)
     obj = hvd.broadcast_object({"r": rank}, 0)
+    # the TensorFlow-flavoured entry points: ranks start with different weights and BN statistics, the hook aligns them
+    bn = nn.BatchNorm2d(4).to(dev)
+    with torch.no_grad():
+        bn.weight.fill_(float(rank + 2))
+        bn.running_mean.fill_(float(rank + 5))
+    hook = hvd.BroadcastGlobalVariablesHook(0)
+    hook.begin(bn)
+    hook.begin(bn)                             # idempotent
+    assert hook.done and float(bn.weight[0]) == 2.0 and float(bn.running_mean[0]) == 5.0, (bn.weight, bn.running_mean)
     return (s.cpu().tolist(), a.cpu().tolist(), g.shape[0], b.cpu().tolist(), z.cpu().tolist(), obj)
 
 
