@@ -10,6 +10,16 @@ _REGISTRY = {
     "resnet50_v1.5": resnet.resnet50_v15,
     "resnet101": resnet.resnet101,
     "resnet152": resnet.resnet152,
+    # the TF official-models ResNets tf_cnn_benchmarks exposes as official_resnet*: 18 / 34 are basic-block networks,
+    # 50 / 101 / 152 are the v1.5 form (stride in the 3x3), the _v2 names the pre-activation form
+    "official_resnet18": resnet.official_resnet18,
+    "official_resnet34": resnet.official_resnet34,
+    "official_resnet50": lambda cfg: resnet.ResNet(cfg, (3, 4, 6, 3), True, "official_resnet50"),
+    "official_resnet101": lambda cfg: resnet.ResNet(cfg, (3, 4, 23, 3), True, "official_resnet101"),
+    "official_resnet152": lambda cfg: resnet.ResNet(cfg, (3, 8, 36, 3), True, "official_resnet152"),
+    "official_resnet50_v2": lambda cfg: zoo2.ResNetV2(cfg, (3, 4, 6, 3), "official_resnet50_v2"),
+    "official_resnet101_v2": lambda cfg: zoo2.ResNetV2(cfg, (3, 4, 23, 3), "official_resnet101_v2"),
+    "official_resnet152_v2": lambda cfg: zoo2.ResNetV2(cfg, (3, 8, 36, 3), "official_resnet152_v2"),
     "vgg11": lambda cfg: zoo.VGG(cfg, (1, 1, 2, 2, 2), "vgg11"),
     "vgg16": lambda cfg: zoo.VGG(cfg, (2, 2, 3, 3, 3), "vgg16"),
     "vgg19": lambda cfg: zoo.VGG(cfg, (2, 2, 4, 4, 4), "vgg19"),

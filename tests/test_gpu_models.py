@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 MODELS = ["resnet50", "resnet50_v1.5", "resnet50_v2", "vgg11", "inception3", "inception4", "googlenet", "alexnet",
-          "overfeat", "lenet", "trivial", "resnet20", "resnet20_v2", "densenet40_k12", "mobilenet", "nasnet"]
+          "overfeat", "lenet", "trivial", "resnet20", "resnet20_v2", "densenet40_k12", "mobilenet", "nasnet", "official_resnet18", "official_resnet34"]
 
 
 @pytest.mark.parametrize("name", MODELS)

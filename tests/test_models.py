@@ -16,6 +16,8 @@ EXPECTED_PARAMS = {          # trainable parameters with 1001 classes
     # NASNet-A: the published Keras / slim sizes are 5,289,978 (mobile) and 88,753,150 (large) trainable parameters
     # with 1000 classes; the 1001st class adds 1056 + 1 and 4032 + 1
     "nasnet": 5289978 + 1057, "nasnetlarge": 88753150 + 4033,
+    # TF official-models ResNets: the published 11,689,512 / 21,797,672 / 25,557,032 (1000 classes) + the 1001st class
+    "official_resnet18": 11689512 + 513, "official_resnet34": 21797672 + 513, "official_resnet50": 25557032 + 2049,
     # CIFAR-10 models (11 classes): the published sizes are 0.27 M / 0.85 M / 1.7 M (ResNet-20/56/110) and
     # 1.0 M / 7.0 M / 27.2 M (DenseNet 40-k12 / 100-k12 / 100-k24)
     "resnet20": 269787, "resnet56": 853083, "resnet110": 1728027, "resnet20_v2": 269787,
@@ -37,7 +39,7 @@ def test_resnet50_has_161_trainable_tensors_and_53_convs():
 
 
 @pytest.mark.parametrize("name", ["resnet50", "googlenet", "lenet", "trivial", "resnet50_v2", "resnet20", "resnet32_v2",
-                                  "densenet40_k12", "inception4", "mobilenet", "nasnet"])
+                                  "densenet40_k12", "inception4", "mobilenet", "nasnet", "official_resnet18"])
 def test_forward_backward_shapes(name):
     m = create_model(name)
     x = torch.randn(2, 3, m.image_size, m.image_size).contiguous(memory_format=torch.channels_last)
